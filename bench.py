@@ -1,0 +1,379 @@
+#!/usr/bin/env python3
+"""bench.py — headline benchmark of the B200 validation workload (BASELINE.json configs[1]).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+A step is one pass of the hot path over one batch: ONE launch of the fp32 vectorAdd kernel
+(C = A + B, N = 2^28 elements, 3 x 1 GiB arrays) per GPU, through the C ABI (b200v_add_f32).
+Inputs are synthetic (index-hash generator, filled on the device before the timed region) and
+the three arrays are 3 GiB >> the 126 MB L2, so no L2 flush is needed between launches.
+With N GPUs every rank runs the same per-GPU workload on its own device (weak scaling, no
+data-path collective: the vectors shard with no communication); torch.distributed/NCCL is used
+only for the barrier and the max-over-ranks of the device-timed durations.
+
+One JSON line on stdout (rank 0).  `value` = whole-job GB/s of algorithmic bytes (12 B/element);
+`e2e` = the same metric through b200v_vector_add_host with pinned HOST buffers (H2D + kernel +
+D2H inside the timed region); `roofline` = the add kernel against the measured HBM copy peak;
+`cpu_baseline` = the oracle's OpenMP loop on this box's host cores (a reported baseline).
+`--impl reference` times that CPU loop as the reference arm: the reference repo itself has no
+compute code for this path (its Step 9 pod runs `nvidia-smi`), so the CPU restatement in oracle/
+is the reference implementation.
+"""
+import argparse
+import ctypes as C
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+METRIC = "vectorAdd/triad HBM GB/s per GPU & node at 1/2/4/8 B200, % of ~8 TB/s peak"
+LOG2_N = 28
+N_ELEMS = 1 << LOG2_N
+BYTES_PER_STEP = 12 * N_ELEMS          # 12 B per fp32 element for add/triad
+NOMINAL_GBS = 8000.0
+FALLBACK_GBS = 6650.0                  # B200_PROFILING.md fallback when MEASURED_PEAKS.json is absent
+SEED = 20261106
+CPU_SAMPLE_LOG2 = 26                   # elements per CPU step in the reference arm / cpu_baseline
+
+
+def measured_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (of measured)"
+    except Exception:
+        return FALLBACK_GBS, "B200_PROFILING.md fallback 6.65 TB/s (of fallback)"
+
+
+def ncu_traffic_per_launch():
+    """dram__bytes_read.sum + dram__bytes_write.sum of one add launch, from the committed ncu capture."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            return json.load(f)["add_f32_2p28"]["dram_bytes_per_launch"]
+    except Exception:
+        return None
+
+
+# ------------------------------------------------------------------------------------------------
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons of one GPU through NVML while the timed region runs."""
+
+    REASONS = {0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown",
+               0x40: "hw_thermal_slowdown", 0x80: "hw_power_brake"}
+
+    def __init__(self, uuid, period=0.005):
+        super().__init__(daemon=True)
+        self.period = period
+        self.samples = []          # (t, sm_mhz, reasons_mask, power_w)
+        self.marks = {}
+        self.stop_flag = False
+        self.ok = False
+        self.sm_max = None
+        try:
+            import pynvml
+            self.nv = pynvml
+            pynvml.nvmlInit()
+            try:
+                self.h = pynvml.nvmlDeviceGetHandleByUUID(uuid.encode() if isinstance(uuid, str) else uuid)
+            except Exception:
+                self.h = pynvml.nvmlDeviceGetHandleByIndex(0)
+            self.sm_max = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception as e:  # NVML not loadable: report that, never invent clocks
+            self.err = repr(e)
+
+    def run(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        while not self.stop_flag:
+            try:
+                mhz = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
+                try:
+                    mask = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                try:
+                    pw = nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0
+                except Exception:
+                    pw = None
+                self.samples.append((time.perf_counter(), mhz, mask, pw))
+            except Exception:
+                pass
+            time.sleep(self.period)
+
+    def mark(self, name):
+        self.marks[name] = time.perf_counter()
+
+    def summary(self):
+        if not self.ok:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "note": "NVML unavailable: " + getattr(self, "err", "")}
+        t0, t1 = self.marks.get("timed_start", 0), self.marks.get("timed_end", float("inf"))
+        inside = [s for s in self.samples if t0 <= s[0] <= t1]
+        window = "timed region"
+        if len(inside) < 3:   # very short timed region: widen to warm-up .. end of the device-timed legs
+            inside = [s for s in self.samples if self.marks.get("load_start", 0) <= s[0] <= self.marks.get("load_end", t1)]
+            window = "warm-up + timed + triad legs (timed region shorter than 3 samples)"
+        if not inside:
+            inside = self.samples
+        mhz = sorted(s[1] for s in inside)
+        mask = 0
+        for s in inside:
+            mask |= s[2]
+        pw = [s[3] for s in inside if s[3] is not None]
+        return {"sm_mhz": mhz[len(mhz) // 2] if mhz else None, "sm_max_mhz": self.sm_max,
+                "reasons": [n for b, n in self.REASONS.items() if mask & b],
+                "power_w_max": max(pw) if pw else None, "samples": len(inside), "window": window}
+
+
+# ------------------------------------------------------------------------------------------------
+def cpu_step_runner(log2n):
+    """Returns (run_one_step, cores, n): the oracle's OpenMP vectorAdd on host memory."""
+    import numpy as np
+    import oracle_lib as O
+    n = 1 << log2n
+    a = O.fill("f32", 0, n, SEED, 0)
+    b = O.fill("f32", 0, n, SEED, 1)
+    c = np.zeros(n, dtype=np.uint32)
+    L = O.lib()
+    pa, pb, pc = (x.ctypes.data_as(C.c_void_p) for x in (a, b, c))
+
+    def step():
+        L.oracle_add_f32(pc, pa, pb, n, 0)
+
+    step.keep = (a, b, c)
+    return step, L.oracle_max_threads(), n
+
+
+def cpu_baseline(budget_s=10.0):
+    step, cores, n = cpu_step_runner(CPU_SAMPLE_LOG2)
+    step()
+    t0 = time.perf_counter()
+    reps = 0
+    while True:
+        step()
+        reps += 1
+        dt = time.perf_counter() - t0
+        if dt >= budget_s or reps >= 400:
+            break
+    gbs = 12.0 * n * reps / dt * 1e-9
+    return {"value": round(gbs, 2), "unit": "GB/s", "cores": cores, "kind": "port",
+            "sample": f"oracle_add_f32 (OpenMP, -O3 -ffp-contract=off), N=2^{CPU_SAMPLE_LOG2} fp32 per pass, "
+                      f"{reps} passes in {dt:.1f} s; the reference repo has no code for this path, so the port is the baseline"}
+
+
+def run_reference(args, rank):
+    """Reference arm: the CPU implementation of the path on this box's host cores."""
+    if rank != 0:
+        return
+    step, cores, n = cpu_step_runner(CPU_SAMPLE_LOG2)
+    for _ in range(max(args.warmup, 1)):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    dt = time.perf_counter() - t0
+    gbs = 12.0 * n * args.steps / dt * 1e-9
+    sample = (f"each step = oracle_add_f32 (OpenMP, {cores} threads) over N=2^{CPU_SAMPLE_LOG2} fp32 elements resident in "
+              f"host RAM, a bounded sample of the 2^{LOG2_N} workload; GB/s is size-independent for a streaming loop")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": round(gbs, 2), "unit": "GB/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(dt / args.steps * 1e3, 4),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"vectorAdd fp32 C=A+B, N=2^{LOG2_N} per GPU (BASELINE.json configs[1]); CPU arm runs a "
+                               f"2^{CPU_SAMPLE_LOG2}-element sample per step", "bytes_per_element": 12},
+        "cpu_baseline": {"value": round(gbs, 2), "unit": "GB/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": round(gbs, 2), "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=1000)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--e2e-steps", type=int, default=8)
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return 0
+
+    pkg = importlib.import_module("kubernetes-with-nvidia-gpu_b200")
+    L = pkg.lib()          # raises if libb200v.so is missing: no fallback
+    pkg.check(L.b200v_set_device(local_rank))
+    pkg.check(L.b200v_require_sm100(local_rank))
+    info = pkg.device_info(local_rank)
+
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        pkg.check(L.b200v_device_sync())
+
+    def max_over_ranks(ms):
+        if dist is None:
+            return ms
+        import torch
+        t = torch.tensor([ms], dtype=torch.float64, device=f"cuda:{local_rank}")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    vp = C.c_void_p
+    nbytes = 4 * N_ELEMS
+    dA, dB, dC = (pkg.DeviceBuffer(nbytes) for _ in range(3))
+    # each rank owns the shard [rank*N, (rank+1)*N) of the job's global index space
+    start = rank * N_ELEMS
+    pkg.check(L.b200v_fill(pkg.F32, vp(dA.ptr), start, N_ELEMS, SEED, 0, pkg.GEN_UNIT, None))
+    pkg.check(L.b200v_fill(pkg.F32, vp(dB.ptr), start, N_ELEMS, SEED, 1, pkg.GEN_UNIT, None))
+    stream = vp(None)
+    pkg.check(L.b200v_stream_create(C.byref(stream)))
+    ev0, ev1 = vp(None), vp(None)
+    pkg.check(L.b200v_event_create(C.byref(ev0)))
+    pkg.check(L.b200v_event_create(C.byref(ev1)))
+
+    sampler = ClockSampler(info.uuid.decode())
+    sampler.start()
+
+    def timed(fn, steps):
+        barrier()
+        pkg.check(L.b200v_event_record(ev0, stream))
+        for _ in range(steps):
+            fn()
+        pkg.check(L.b200v_event_record(ev1, stream))
+        pkg.check(L.b200v_event_sync(ev1))
+        barrier()
+        ms = C.c_float(0)
+        pkg.check(L.b200v_event_elapsed_ms(ev0, ev1, C.byref(ms)))
+        return ms.value
+
+    add = lambda: pkg.check(L.b200v_add_f32(vp(dC.ptr), vp(dA.ptr), vp(dB.ptr), N_ELEMS, stream))
+    triad = lambda: pkg.check(L.b200v_triad_f32(vp(dC.ptr), 3.0, vp(dA.ptr), vp(dB.ptr), N_ELEMS, stream))
+
+    # ---- device-resident leg (value): W warm-up steps, then exactly K timed steps ----
+    sampler.mark("load_start")
+    for _ in range(args.warmup):
+        add()
+    sampler.mark("timed_start")
+    ms_local = timed(add, args.steps)
+    sampler.mark("timed_end")
+    ms_total = max_over_ranks(ms_local)
+    ms_per_step = ms_total / args.steps
+    value = world * BYTES_PER_STEP / ms_per_step * 1e-6
+
+    # the north-star kernel (triad, same 12 B/element) as a second, separately timed line
+    for _ in range(args.warmup):
+        triad()
+    triad_steps = max(min(args.steps, 200), 3)
+    triad_ms = max_over_ranks(timed(triad, triad_steps)) / triad_steps
+    sampler.mark("load_end")
+    triad_gbs_per_gpu = BYTES_PER_STEP / triad_ms * 1e-6
+
+    # cheap in-run parity check of what was just timed: device checksum vs the oracle on a window
+    import numpy as np
+    import oracle_lib as O
+    add()
+    pkg.check(L.b200v_stream_sync(stream))
+    w = 1 << 16
+    got = dC.download(np.uint32, w, 4 * (N_ELEMS - w))
+    want = O.op("add", "f32", w, x=O.fill("f32", start + N_ELEMS - w, w, SEED, 0), y=O.fill("f32", start + N_ELEMS - w, w, SEED, 1))
+    parity_ok = bool((got == want).all())
+
+    # ---- end-to-end leg: host buffers through the public call, copies inside the timed region ----
+    for b in (dA, dB, dC):
+        b.free()
+    hA, hB, hC = (pkg.PinnedBuffer(nbytes) for _ in range(3))
+    va, vb, vc = (h.view(np.uint32) for h in (hA, hB, hC))
+    O.lib().oracle_fill_f32(vp(hA.ptr), start, N_ELEMS, SEED, 0, O.GEN_UNIT)
+    O.lib().oracle_fill_f32(vp(hB.ptr), start, N_ELEMS, SEED, 1, O.GEN_UNIT)
+    e2e_call = lambda: pkg.check(L.b200v_vector_add_host(vp(hA.ptr), vp(hB.ptr), vp(hC.ptr), N_ELEMS))
+    e2e_call()   # warm-up: allocates the staging buffers
+    e2e_call()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.e2e_steps):
+        e2e_call()     # synchronous: returns when hC is complete in host memory
+    e2e_ms_local = (time.perf_counter() - t0) * 1e3
+    barrier()
+    e2e_ms = max_over_ranks(e2e_ms_local) / args.e2e_steps
+    e2e_value = world * BYTES_PER_STEP / e2e_ms * 1e-6
+    w0 = N_ELEMS // 2
+    e2e_ok = bool((vc[w0:w0 + w] == O.op("add", "f32", w, x=np.ascontiguousarray(va[w0:w0 + w]), y=np.ascontiguousarray(vb[w0:w0 + w]))).all())
+    pkg.check(L.b200v_vector_add_host_release())
+    del va, vb, vc
+    for h in (hA, hB, hC):
+        h.free()
+
+    sampler.stop_flag = True
+    sampler.join(timeout=2)
+
+    if dist is not None:
+        dist.barrier()
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return 0
+
+    peak, peak_src = measured_peak()
+    achieved = BYTES_PER_STEP / (ms_local / args.steps) * 1e-6     # rank 0's add kernel, GB/s
+    line = {
+        "metric": METRIC, "value": round(value, 1), "unit": "GB/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": round(ms_per_step, 5), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {
+            "workload": f"vectorAdd fp32 C=A+B, N=2^{LOG2_N} elements per GPU (BASELINE.json configs[1]), one kernel launch per step",
+            "bytes_per_step_per_gpu": BYTES_PER_STEP, "bytes_per_element": 12, "parallelism": f"shard{world} (no collective)",
+            "l2": "inputs are 3 GiB per GPU, far larger than the 126 MB L2: no flush between steps",
+            "gpu": info.name.decode(), "sm_count": info.sm_count,
+        },
+        "roofline": {
+            "bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
+            "frac": round(achieved / peak, 4), "traffic": ncu_traffic_per_launch(),
+            "peak_source": peak_src, "kernel": "b200v::stream_kernel<OP_ADD,f32> via b200v_add_f32",
+            "algorithmic_bytes_per_launch": BYTES_PER_STEP,
+            "frac_of_nominal_8000": round(achieved / NOMINAL_GBS, 4),
+        },
+        "triad": {"gbs_per_gpu": round(triad_gbs_per_gpu, 1), "ms_per_step": round(triad_ms, 5), "steps": triad_steps,
+                  "frac_of_measured": round(triad_gbs_per_gpu / peak, 4),
+                  "frac_of_nominal_8000": round(triad_gbs_per_gpu / NOMINAL_GBS, 4),
+                  "node_gbs": round(world * triad_gbs_per_gpu, 1)},
+        "e2e": {"value": round(e2e_value, 2), "unit": "GB/s", "h2d_bytes_per_step": 8 * N_ELEMS * world,
+                "d2h_bytes_per_step": 4 * N_ELEMS * world, "ms_per_step": round(e2e_ms, 3), "steps": args.e2e_steps,
+                "api": "b200v_vector_add_host(hA, hB, hC, n) with pinned host buffers; host wall clock around the synchronous call"},
+        "gpu_launches": args.steps * world, "gpu_launches_per_rank": args.steps,
+        "parity": {"device_window_bit_exact": parity_ok, "e2e_window_bit_exact": e2e_ok},
+        "clocks": sampler.summary(),
+    }
+    if not args.no_cpu:
+        line["cpu_baseline"] = cpu_baseline()
+    print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+    return 0 if (parity_ok and e2e_ok) else 1
+
+
+if __name__ == "__main__":
+    sys.exit(main())

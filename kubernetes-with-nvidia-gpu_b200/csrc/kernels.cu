@@ -1,0 +1,475 @@
+// kernels.cu — device code of libb200v and the C-ABI entry points that launch it:
+// the streaming kernels (add/copy/scale/triad, fp32 + bf16), the index-hash fill, the
+// checksum reduction, and the peer-pull copy.  See include/b200v.h for the contract and the
+// reference lines each group stands in for.
+#include <cstdint>
+#include <cstring>
+
+#include "internal.h"
+#include "stream_kernels.cuh"
+#include "tuning.h"
+
+namespace b200v {
+
+// ------------------------------------------------------------------------------------------
+// device properties the launch shapes need, cached per device
+
+struct DevCache {
+    bool known = false;
+    int sm_count = 0;
+};
+static DevCache g_dev[64];
+
+static int current_sm_count(int* sms)
+{
+    int dev = 0;
+    B200V_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return set_error(B200V_ERR_INVALID, "device index %d out of range", dev);
+    if (!g_dev[dev].known) {
+        int n = 0, major = 0;
+        B200V_CUDA(cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev));
+        B200V_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
+        if (major != 10)
+            return set_error(B200V_ERR_ARCH, "device %d is compute capability %d.x; libb200v carries sm_100a code only", dev, major);
+        g_dev[dev].sm_count = n;
+        g_dev[dev].known = true;
+    }
+    *sms = g_dev[dev].sm_count;
+    return B200V_OK;
+}
+
+static bool overlaps(const void* a, size_t abytes, const void* b, size_t bbytes)
+{
+    uintptr_t a0 = (uintptr_t)a, b0 = (uintptr_t)b;
+    return a0 < b0 + bbytes && b0 < a0 + abytes;
+}
+
+// ------------------------------------------------------------------------------------------
+// streaming ops
+
+template <int OP, bool BF16, int VECB, int UNROLL, int BLOCK>
+static int launch_vec(void* dst, const void* x, const void* y, float s, size_t n, int sms, cudaStream_t st)
+{
+    constexpr size_t EPW = BF16 ? 2 : 1;
+    constexpr size_t TILE_ELEMS = (size_t)BLOCK * UNROLL * (VECB / 4) * EPW;
+    size_t tiles = n / TILE_ELEMS;
+    size_t grid = tiles ? tiles : 1;
+    if (Tuning::kCtasPerSm > 0) {
+        size_t cap = (size_t)sms * Tuning::kCtasPerSm;
+        if (grid > cap) grid = cap;
+    }
+    if (grid > 0x7FFFFFFFull) grid = 0x7FFFFFFFull;
+    stream_kernel<OP, BF16, VECB, UNROLL, BLOCK, Tuning::kLd, Tuning::kSt>
+        <<<(unsigned)grid, BLOCK, 0, st>>>(dst, x, y, s, n);
+    B200V_CUDA(cudaGetLastError());
+    return B200V_OK;
+}
+
+template <int OP, bool BF16>
+static int launch_stream(void* dst, const void* x, const void* y, float s, size_t n, cudaStream_t st)
+{
+    constexpr size_t ESZ = BF16 ? 2 : 4;
+    constexpr bool TWO = kReadsY<OP>;
+    B200V_REQUIRE(dst && x && (!TWO || y), B200V_ERR_INVALID, "NULL array pointer");
+    if (n == 0) return B200V_OK;
+    uintptr_t bits = (uintptr_t)dst | (uintptr_t)x | (TWO ? (uintptr_t)y : 0);
+    B200V_REQUIRE(bits % ESZ == 0, B200V_ERR_ALIGN, "array pointer not aligned to its %zu-byte element", ESZ);
+    B200V_REQUIRE(!overlaps(dst, n * ESZ, x, n * ESZ) && (!TWO || !overlaps(dst, n * ESZ, y, n * ESZ)),
+                  B200V_ERR_INVALID, "output array overlaps an input array (STREAM arrays are distinct)");
+    int sms = 0;
+    if (int rc = current_sm_count(&sms)) return rc;
+
+    constexpr int BLOCK = TWO ? Tuning::kBlock2 : Tuning::kBlock1;
+    constexpr int UNROLL = TWO ? Tuning::kUnroll2 : Tuning::kUnroll1;
+    if (bits % 32 == 0) return launch_vec<OP, BF16, 32, UNROLL, BLOCK>(dst, x, y, s, n, sms, st);
+    if (bits % 16 == 0) return launch_vec<OP, BF16, 16, UNROLL * 2, BLOCK>(dst, x, y, s, n, sms, st);
+    size_t grid = (n + 255) / 256;
+    size_t cap = (size_t)sms * 32;
+    if (grid > cap) grid = cap;
+    stream_kernel_unaligned<OP, BF16><<<(unsigned)grid, 256, 0, st>>>(dst, x, y, s, n);
+    B200V_CUDA(cudaGetLastError());
+    return B200V_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// fill: the index-hash generator (same integer spec as oracle/oracle.c and csrc/hostcheck.cpp)
+
+__host__ __device__ __forceinline__ uint32_t mix32(uint32_t x)
+{
+    x ^= x >> 16;
+    x *= 0x7FEB352Du;
+    x ^= x >> 15;
+    x *= 0x846CA68Bu;
+    x ^= x >> 16;
+    return x;
+}
+
+__host__ __device__ __forceinline__ uint32_t hash32(uint32_t key, uint64_t index)
+{
+    return mix32((uint32_t)index ^ key ^ ((uint32_t)(index >> 32) * 0x9E3779B9u));
+}
+
+__device__ __forceinline__ uint32_t gen_f32_bits(uint32_t key, uint64_t index, int mode)
+{
+    uint32_t h = hash32(key, index);
+    if (mode == B200V_GEN_UNIT) return __float_as_uint(__fmul_rn((float)(h >> 8), 0x1p-24f));
+    if (mode == B200V_GEN_DENORM) return h & 0x81FFFFFFu;
+    if ((h & 0x7F800000u) == 0x7F800000u) h &= ~0x00800000u;
+    return h;
+}
+
+__device__ __forceinline__ uint32_t gen_bf16_bits(uint32_t key, uint64_t index, int mode)
+{
+    uint32_t h = hash32(key, index);
+    if (mode == B200V_GEN_UNIT) return __float_as_uint(__fmul_rn((float)(h >> 24), 0x1p-8f)) >> 16;
+    uint32_t b = h >> 16;
+    if (mode == B200V_GEN_DENORM) return b & 0x81FFu;
+    if ((b & 0x7F80u) == 0x7F80u) b &= ~0x0080u;
+    return b;
+}
+
+// One thread produces 16 bytes (4 fp32 / 8 bf16) where dst is 16-byte aligned; the ragged
+// head and tail are written element-wise.
+template <bool BF16>
+__global__ void __launch_bounds__(256)
+fill_kernel(void* __restrict__ dst, uint64_t start, size_t n, uint32_t key, int mode)
+{
+    constexpr size_t EPV = BF16 ? 8 : 4;
+    constexpr size_t ESZ = BF16 ? 2 : 4;
+    size_t head = ((16 - ((uintptr_t)dst & 15)) & 15) / ESZ;
+    if (head > n) head = n;
+    const size_t nvec = (n - head) / EPV;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint4* vdst = reinterpret_cast<uint4*>(reinterpret_cast<char*>(dst) + head * ESZ);
+    for (size_t v = tid; v < nvec; v += stride) {
+        const uint64_t i0 = start + head + v * EPV;
+        uint4 o;
+        if constexpr (!BF16) {
+            o.x = gen_f32_bits(key, i0 + 0, mode);
+            o.y = gen_f32_bits(key, i0 + 1, mode);
+            o.z = gen_f32_bits(key, i0 + 2, mode);
+            o.w = gen_f32_bits(key, i0 + 3, mode);
+        } else {
+            o.x = gen_bf16_bits(key, i0 + 0, mode) | (gen_bf16_bits(key, i0 + 1, mode) << 16);
+            o.y = gen_bf16_bits(key, i0 + 2, mode) | (gen_bf16_bits(key, i0 + 3, mode) << 16);
+            o.z = gen_bf16_bits(key, i0 + 4, mode) | (gen_bf16_bits(key, i0 + 5, mode) << 16);
+            o.w = gen_bf16_bits(key, i0 + 6, mode) | (gen_bf16_bits(key, i0 + 7, mode) << 16);
+        }
+        vdst[v] = o;
+    }
+    // ragged ends: [0, head) and [head + nvec*EPV, n)
+    const size_t tail0 = head + nvec * EPV;
+    const size_t ragged = head + (n - tail0);
+    for (size_t r = tid; r < ragged; r += stride) {
+        const size_t j = r < head ? r : tail0 + (r - head);
+        if constexpr (!BF16) reinterpret_cast<uint32_t*>(dst)[j] = gen_f32_bits(key, start + j, mode);
+        else reinterpret_cast<uint16_t*>(dst)[j] = (uint16_t)gen_bf16_bits(key, start + j, mode);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// checksum: out[0] = sum w_j, out[1] = sum w_j * ((uint32_t)(word_offset + j) | 1)  (mod 2^64)
+//
+// Workspace layout (caller-owned scratch): bytes [0,16): a uint32 arrival counter (zeroed by the
+// entry point before every launch); then one {s0, s1} uint64 pair per CTA.  Every CTA reduces its
+// grid-stride share, publishes its pair, and the last CTA to arrive adds the pairs up.
+
+constexpr int kChecksumBlock = 256;
+constexpr int kChecksumMaxBlocks = 2048;
+constexpr int kChecksumUnroll = 4;
+
+__device__ __forceinline__ uint4 ld_stream_u4(const uint4* p)
+{
+    uint4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.b32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                 : "l"(p));
+    return v;
+}
+
+__device__ __forceinline__ void acc_word(uint64_t& s0, uint64_t& s1, uint32_t w, uint64_t j)
+{
+    s0 += w;
+    s1 += (uint64_t)w * (uint64_t)((uint32_t)j | 1u);
+}
+
+__global__ void __launch_bounds__(kChecksumBlock)
+checksum_kernel(const unsigned char* __restrict__ buf, size_t nbytes, uint64_t word_offset,
+                unsigned int* __restrict__ counter, uint64_t* __restrict__ partials, uint64_t* __restrict__ out)
+{
+    const size_t nwords = nbytes / 4;
+    const uint32_t* words = reinterpret_cast<const uint32_t*>(buf);
+    size_t head = ((16 - ((uintptr_t)buf & 15)) & 15) / 4;   // words before 16-byte alignment
+    if (head > nwords) head = nwords;
+    const size_t nvec = (nwords - head) / 4;
+    const uint4* vec = reinterpret_cast<const uint4*>(words + head);
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+
+    uint64_t s0 = 0, s1 = 0;
+    size_t v = tid;
+    for (; v + (kChecksumUnroll - 1) * stride < nvec; v += kChecksumUnroll * stride) {
+        uint4 q[kChecksumUnroll];
+#pragma unroll
+        for (int u = 0; u < kChecksumUnroll; ++u) q[u] = ld_stream_u4(vec + v + u * stride);
+#pragma unroll
+        for (int u = 0; u < kChecksumUnroll; ++u) {
+            const uint64_t j = word_offset + head + (v + u * stride) * 4;
+            acc_word(s0, s1, q[u].x, j + 0);
+            acc_word(s0, s1, q[u].y, j + 1);
+            acc_word(s0, s1, q[u].z, j + 2);
+            acc_word(s0, s1, q[u].w, j + 3);
+        }
+    }
+    for (; v < nvec; v += stride) {
+        uint4 q = ld_stream_u4(vec + v);
+        const uint64_t j = word_offset + head + v * 4;
+        acc_word(s0, s1, q.x, j + 0);
+        acc_word(s0, s1, q.y, j + 1);
+        acc_word(s0, s1, q.z, j + 2);
+        acc_word(s0, s1, q.w, j + 3);
+    }
+    // ragged words: [0, head) and [head + 4*nvec, nwords), then the 1..3 trailing bytes
+    const size_t tail0 = head + nvec * 4;
+    const size_t ragged = head + (nwords - tail0);
+    for (size_t r = tid; r < ragged; r += stride) {
+        const size_t j = r < head ? r : tail0 + (r - head);
+        acc_word(s0, s1, words[j], word_offset + j);
+    }
+    if (tid == 0 && (nbytes & 3)) {
+        uint32_t w = 0;
+        for (size_t k = 0; k < (nbytes & 3); ++k) w |= (uint32_t)buf[nwords * 4 + k] << (8 * k);
+        acc_word(s0, s1, w, word_offset + nwords);
+    }
+
+    // CTA reduction
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        s0 += __shfl_down_sync(0xFFFFFFFFu, s0, d);
+        s1 += __shfl_down_sync(0xFFFFFFFFu, s1, d);
+    }
+    __shared__ uint64_t sh0[kChecksumBlock / 32], sh1[kChecksumBlock / 32];
+    __shared__ bool last;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) { sh0[warp] = s0; sh1[warp] = s1; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint64_t t0 = 0, t1 = 0;
+#pragma unroll
+        for (int w = 0; w < kChecksumBlock / 32; ++w) { t0 += sh0[w]; t1 += sh1[w]; }
+        partials[2 * blockIdx.x + 0] = t0;
+        partials[2 * blockIdx.x + 1] = t1;
+        __threadfence();
+        last = (atomicAdd(counter, 1u) == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!last) return;
+    __threadfence();
+    uint64_t t0 = 0, t1 = 0;
+    for (unsigned b = threadIdx.x; b < gridDim.x; b += kChecksumBlock) {
+        t0 += __ldcg(&partials[2 * b + 0]);
+        t1 += __ldcg(&partials[2 * b + 1]);
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        t0 += __shfl_down_sync(0xFFFFFFFFu, t0, d);
+        t1 += __shfl_down_sync(0xFFFFFFFFu, t1, d);
+    }
+    __syncthreads();
+    if (lane == 0) { sh0[warp] = t0; sh1[warp] = t1; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint64_t r0 = 0, r1 = 0;
+#pragma unroll
+        for (int w = 0; w < kChecksumBlock / 32; ++w) { r0 += sh0[w]; r1 += sh1[w]; }
+        out[0] = r0;
+        out[1] = r1;
+        *counter = 0;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// peer pull: this device's SMs read a peer's buffer over NVLink with 256-bit loads (peer
+// addresses bypass the local L2, so no cache hint is asked for) and write local HBM.
+
+constexpr int kPullBlock = 512;
+constexpr int kPullUnroll = 4;
+
+__global__ void __launch_bounds__(kPullBlock)
+peer_pull_kernel(Vec<32>* __restrict__ dst, const Vec<32>* __restrict__ src, size_t nvec)
+{
+    constexpr size_t TILE = (size_t)kPullBlock * kPullUnroll;
+    const size_t tiles = nvec / TILE;
+    for (size_t t = blockIdx.x; t < tiles; t += gridDim.x) {
+        const size_t base = t * TILE + threadIdx.x;
+        Vec<32> v[kPullUnroll];
+#pragma unroll
+        for (int u = 0; u < kPullUnroll; ++u) v[u] = ldg<LD_DEFAULT>(src + base + (size_t)u * kPullBlock);
+#pragma unroll
+        for (int u = 0; u < kPullUnroll; ++u) stg<ST_DEFAULT>(dst + base + (size_t)u * kPullBlock, v[u]);
+    }
+    if (blockIdx.x == tiles % gridDim.x)
+        for (size_t i = tiles * TILE + threadIdx.x; i < nvec; i += kPullBlock)
+            stg<ST_DEFAULT>(dst + i, ldg<LD_DEFAULT>(src + i));
+}
+
+__global__ void __launch_bounds__(256)
+byte_copy_kernel(unsigned char* __restrict__ dst, const unsigned char* __restrict__ src, size_t n)
+{
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) dst[i] = src[i];
+}
+
+}  // namespace b200v
+
+// ==========================================================================================
+// C ABI
+// ==========================================================================================
+using namespace b200v;
+
+extern "C" {
+
+int b200v_stream_op(int op, int dtype, void* dst, const void* x, const void* y, float s, size_t n, void* stream)
+{
+    cudaStream_t st = as_stream(stream);
+    B200V_REQUIRE(dtype == B200V_F32 || dtype == B200V_BF16, B200V_ERR_INVALID, "unknown dtype %d", dtype);
+    const bool bf = dtype == B200V_BF16;
+    switch (op) {
+    case B200V_OP_ADD:
+        return bf ? launch_stream<OP_ADD, true>(dst, x, y, s, n, st) : launch_stream<OP_ADD, false>(dst, x, y, s, n, st);
+    case B200V_OP_COPY:
+        return bf ? launch_stream<OP_COPY, true>(dst, x, y, s, n, st) : launch_stream<OP_COPY, false>(dst, x, y, s, n, st);
+    case B200V_OP_SCALE:
+        return bf ? launch_stream<OP_SCALE, true>(dst, x, y, s, n, st) : launch_stream<OP_SCALE, false>(dst, x, y, s, n, st);
+    case B200V_OP_TRIAD:
+        return bf ? launch_stream<OP_TRIAD, true>(dst, x, y, s, n, st) : launch_stream<OP_TRIAD, false>(dst, x, y, s, n, st);
+    default:
+        return set_error(B200V_ERR_INVALID, "unknown op %d", op);
+    }
+}
+
+int b200v_add_f32(float* c, const float* a, const float* b, size_t n, void* stream)
+{
+    return launch_stream<OP_ADD, false>(c, a, b, 0.0f, n, as_stream(stream));
+}
+int b200v_copy_f32(float* c, const float* a, size_t n, void* stream)
+{
+    return launch_stream<OP_COPY, false>(c, a, nullptr, 0.0f, n, as_stream(stream));
+}
+int b200v_scale_f32(float* b, float s, const float* c, size_t n, void* stream)
+{
+    return launch_stream<OP_SCALE, false>(b, c, nullptr, s, n, as_stream(stream));
+}
+int b200v_triad_f32(float* a, float s, const float* c, const float* b, size_t n, void* stream)
+{
+    return launch_stream<OP_TRIAD, false>(a, c, b, s, n, as_stream(stream));
+}
+int b200v_add_bf16(uint16_t* c, const uint16_t* a, const uint16_t* b, size_t n, void* stream)
+{
+    return launch_stream<OP_ADD, true>(c, a, b, 0.0f, n, as_stream(stream));
+}
+int b200v_copy_bf16(uint16_t* c, const uint16_t* a, size_t n, void* stream)
+{
+    return launch_stream<OP_COPY, true>(c, a, nullptr, 0.0f, n, as_stream(stream));
+}
+int b200v_scale_bf16(uint16_t* b, float s, const uint16_t* c, size_t n, void* stream)
+{
+    return launch_stream<OP_SCALE, true>(b, c, nullptr, s, n, as_stream(stream));
+}
+int b200v_triad_bf16(uint16_t* a, float s, const uint16_t* c, const uint16_t* b, size_t n, void* stream)
+{
+    return launch_stream<OP_TRIAD, true>(a, c, b, s, n, as_stream(stream));
+}
+
+uint64_t b200v_op_bytes(int op, int dtype, size_t n)
+{
+    uint64_t esz = dtype == B200V_BF16 ? 2 : 4;
+    uint64_t arrays = (op == B200V_OP_ADD || op == B200V_OP_TRIAD) ? 3 : 2;
+    return arrays * esz * (uint64_t)n;
+}
+
+int b200v_fill(int dtype, void* d_dst, uint64_t start, size_t n, uint32_t seed, uint32_t stream_id, int mode, void* stream)
+{
+    B200V_REQUIRE(dtype == B200V_F32 || dtype == B200V_BF16, B200V_ERR_INVALID, "unknown dtype %d", dtype);
+    B200V_REQUIRE(mode >= B200V_GEN_UNIT && mode <= B200V_GEN_DENORM, B200V_ERR_INVALID, "unknown generator mode %d", mode);
+    B200V_REQUIRE(d_dst != nullptr, B200V_ERR_INVALID, "NULL destination");
+    if (n == 0) return B200V_OK;
+    const size_t esz = dtype == B200V_BF16 ? 2 : 4;
+    B200V_REQUIRE((uintptr_t)d_dst % esz == 0, B200V_ERR_ALIGN, "destination not aligned to its %zu-byte element", esz);
+    int sms = 0;
+    if (int rc = current_sm_count(&sms)) return rc;
+    const uint32_t key = mix32(seed ^ (0x9E3779B9u * (stream_id + 1u)));
+    const size_t epv = dtype == B200V_BF16 ? 8 : 4;
+    size_t grid = (n / epv + 255) / 256 + 1;
+    const size_t cap = (size_t)sms * 16;
+    if (grid > cap) grid = cap;
+    if (dtype == B200V_BF16)
+        fill_kernel<true><<<(unsigned)grid, 256, 0, as_stream(stream)>>>(d_dst, start, n, key, mode);
+    else
+        fill_kernel<false><<<(unsigned)grid, 256, 0, as_stream(stream)>>>(d_dst, start, n, key, mode);
+    B200V_CUDA(cudaGetLastError());
+    return B200V_OK;
+}
+
+size_t b200v_checksum_workspace_bytes(void) { return 16 + (size_t)kChecksumMaxBlocks * 16; }
+
+int b200v_checksum(const void* d_buf, size_t nbytes, uint64_t word_offset, void* d_workspace, size_t workspace_bytes,
+                   uint64_t* d_out, void* stream)
+{
+    B200V_REQUIRE(d_workspace && d_out, B200V_ERR_INVALID, "NULL workspace or output");
+    B200V_REQUIRE(d_buf || nbytes == 0, B200V_ERR_INVALID, "NULL buffer");
+    B200V_REQUIRE(workspace_bytes >= b200v_checksum_workspace_bytes(), B200V_ERR_INVALID,
+                  "workspace is %zu bytes, need %zu", workspace_bytes, b200v_checksum_workspace_bytes());
+    B200V_REQUIRE((uintptr_t)d_workspace % 16 == 0 && (uintptr_t)d_out % 8 == 0, B200V_ERR_ALIGN,
+                  "workspace must be 16-byte and output 8-byte aligned");
+    B200V_REQUIRE((uintptr_t)d_buf % 4 == 0, B200V_ERR_ALIGN, "buffer must be 4-byte aligned");
+    int sms = 0;
+    if (int rc = current_sm_count(&sms)) return rc;
+    cudaStream_t st = as_stream(stream);
+    size_t grid = (nbytes / 16 + kChecksumBlock * kChecksumUnroll - 1) / (kChecksumBlock * kChecksumUnroll);
+    size_t cap = (size_t)sms * 8;
+    if (cap > kChecksumMaxBlocks) cap = kChecksumMaxBlocks;
+    if (grid > cap) grid = cap;
+    if (grid == 0) grid = 1;
+    unsigned int* counter = reinterpret_cast<unsigned int*>(d_workspace);
+    uint64_t* partials = reinterpret_cast<uint64_t*>(reinterpret_cast<char*>(d_workspace) + 16);
+    B200V_CUDA(cudaMemsetAsync(counter, 0, 16, st));
+    checksum_kernel<<<(unsigned)grid, kChecksumBlock, 0, st>>>(reinterpret_cast<const unsigned char*>(d_buf), nbytes,
+                                                              word_offset, counter, partials, d_out);
+    B200V_CUDA(cudaGetLastError());
+    return B200V_OK;
+}
+
+int b200v_peer_pull(void* d_local_dst, const void* d_peer_src, size_t bytes, void* stream)
+{
+    B200V_REQUIRE(d_local_dst && d_peer_src, B200V_ERR_INVALID, "NULL pointer");
+    if (bytes == 0) return B200V_OK;
+    int sms = 0;
+    if (int rc = current_sm_count(&sms)) return rc;
+    cudaStream_t st = as_stream(stream);
+    const bool aligned = (((uintptr_t)d_local_dst | (uintptr_t)d_peer_src) % 32) == 0;
+    size_t body = aligned ? (bytes / 32) * 32 : 0;
+    if (body) {
+        size_t nvec = body / 32;
+        size_t grid = nvec / ((size_t)kPullBlock * kPullUnroll);
+        size_t cap = (size_t)sms * 4;
+        if (grid > cap) grid = cap;
+        if (grid == 0) grid = 1;
+        peer_pull_kernel<<<(unsigned)grid, kPullBlock, 0, st>>>(reinterpret_cast<Vec<32>*>(d_local_dst),
+                                                               reinterpret_cast<const Vec<32>*>(d_peer_src), nvec);
+        B200V_CUDA(cudaGetLastError());
+    }
+    if (body < bytes) {
+        size_t rest = bytes - body;
+        size_t grid = (rest + 255) / 256;
+        size_t cap = (size_t)sms * 8;
+        if (grid > cap) grid = cap;
+        byte_copy_kernel<<<(unsigned)grid, 256, 0, st>>>(reinterpret_cast<unsigned char*>(d_local_dst) + body,
+                                                        reinterpret_cast<const unsigned char*>(d_peer_src) + body, rest);
+        B200V_CUDA(cudaGetLastError());
+    }
+    return B200V_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,288 @@
+"""GPU tier: the CUDA path, called through the C ABI, against the CPU oracle — bit-exact.
+
+Everything here goes through libb200v.so (ctypes); the oracle (oracle/liboracle.so) is only the
+checker.  Tolerance: none.  Integer/byte/index work and IEEE fp32/bf16 results must match bit for
+bit (BASELINE.json: "bit-exact against a host C reference loop, triad using explicit fmaf").
+"""
+import ctypes as C
+import json
+import os
+
+import numpy as np
+import pytest
+
+import oracle_lib as O
+from b200v_pkg import pkg
+
+pytestmark = pytest.mark.gpu
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+SEED = 20261106
+M64 = (1 << 64) - 1
+
+
+@pytest.fixture(scope="module")
+def L():
+    L = pkg.lib()
+    assert pkg.device_count() >= 1
+    pkg.check(L.b200v_set_device(0))
+    pkg.check(L.b200v_require_sm100(0))
+    return L
+
+
+def esz(dtype):
+    return 4 if dtype == "f32" else 2
+
+
+def run_op(L, op, dtype, x, y, s=3.0, offset_elems=0):
+    """Upload bit patterns, run one kernel through the ABI, return the output bit patterns.
+    offset_elems shifts every array inside its allocation (alignment cases)."""
+    n = len(x)
+    e = esz(dtype)
+    pad = offset_elems * e
+    dx = pkg.DeviceBuffer(n * e + pad + 64).upload(x, pad)
+    dy = pkg.DeviceBuffer(n * e + pad + 64)
+    if y is not None:
+        dy.upload(y, pad)
+    dd = pkg.DeviceBuffer(n * e + pad + 64)
+    pkg.check(L.b200v_memset(C.c_void_p(dd.ptr), 0xA5, dd.nbytes, None))
+    pkg.stream_op(op, dtype, dd.at(pad), dx.at(pad), dy.at(pad) if y is not None else None, s, n)
+    pkg.check(L.b200v_device_sync())
+    out = dd.download(pkg.NP_BITS[dtype], n, pad)
+    guard = dd.download(np.uint8, 64, pad + n * e)
+    assert (guard == 0xA5).all(), "kernel wrote past the end of its output"
+    if pad:
+        assert (dd.download(np.uint8, pad) == 0xA5).all(), "kernel wrote before the start of its output"
+    for b in (dx, dy, dd):
+        b.free()
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
+def test_discovery(L):
+    info = pkg.device_info(0)
+    assert info.cc_major == 10
+    assert info.sm_count >= 100
+    assert info.hbm_bytes > 100 << 30
+    assert info.l2_bytes > 32 << 20
+    assert info.name and info.uuid.startswith(b"GPU-") and info.pci_bus_id
+    assert info.runtime_version >= 12080 and info.driver_version >= info.runtime_version - 1000
+    n = pkg.device_count()
+    m = (C.c_int * (n * n))()
+    pkg.check(L.b200v_peer_matrix(n, m))
+    assert all(m[i * n + i] == 1 for i in range(n))
+
+
+@pytest.mark.parametrize("dtype", ["f32", "bf16"])
+@pytest.mark.parametrize("mode", [O.GEN_UNIT, O.GEN_BITS, O.GEN_DENORM])
+def test_fill_matches_oracle(L, dtype, mode):
+    e = esz(dtype)
+    for start, n, off in ((0, 1, 0), (0, 50_000, 0), (5, 100_003, 0), ((1 << 32) - 777, 4099, 0),
+                          ((1 << 34) + 1, 1 << 20, 0), (9, 1237, 1), (9, 1237, 3), (0, 7, 5)):
+        buf = pkg.DeviceBuffer(n * e + off * e + 64)
+        pkg.check(L.b200v_memset(C.c_void_p(buf.ptr), 0x5A, buf.nbytes, None))
+        pkg.check(L.b200v_fill(pkg.DTYPES[dtype], buf.at(off * e), start, n, SEED, 3, mode, None))
+        got = buf.download(pkg.NP_BITS[dtype], n, off * e)
+        np.testing.assert_array_equal(got, O.fill(dtype, start, n, SEED, 3, mode))
+        assert (buf.download(np.uint8, 64 - 0, off * e + n * e)[:32] == 0x5A).all()
+        buf.free()
+
+
+SIZES = [1, 2, 7, 31, 50_000, 8191, 8192, 8193, 16384 + 5, (1 << 20) + 3, 3 * (1 << 20) + 12345]
+
+
+@pytest.mark.parametrize("dtype", ["f32", "bf16"])
+@pytest.mark.parametrize("op", ["add", "copy", "scale", "triad"])
+def test_ops_bit_exact(L, op, dtype):
+    for mode in (O.GEN_UNIT, O.GEN_BITS, O.GEN_DENORM):
+        for n in SIZES:
+            x = O.fill(dtype, 11, n, SEED, 0, mode)
+            y = O.fill(dtype, 11, n, SEED, 1, mode)
+            for s in (3.0, -0.333251953125):
+                want = O.op(op, dtype, n, s=s, x=x, y=y)
+                got = run_op(L, op, dtype, x, y if op in ("add", "triad") else None, s)
+                np.testing.assert_array_equal(got, want, err_msg=f"{op} {dtype} mode={mode} n={n} s={s}")
+                if op in ("copy", "add"):
+                    break
+
+
+@pytest.mark.parametrize("dtype", ["f32", "bf16"])
+@pytest.mark.parametrize("offset", [1, 2, 4, 8, 12])
+def test_ops_on_unaligned_views(L, dtype, offset):
+    """Element offsets walk through the scalar (not 16-B aligned), 128-bit and 256-bit paths."""
+    n = 70_001
+    x = O.fill(dtype, 0, n, SEED, 0, O.GEN_BITS)
+    y = O.fill(dtype, 0, n, SEED, 1, O.GEN_BITS)
+    for op in ("add", "copy", "scale", "triad"):
+        want = O.op(op, dtype, n, s=3.0, x=x, y=y)
+        got = run_op(L, op, dtype, x, y if op in ("add", "triad") else None, 3.0, offset_elems=offset)
+        np.testing.assert_array_equal(got, want, err_msg=f"{op} {dtype} offset={offset}")
+
+
+def test_golden_vectors_through_the_gpu(L):
+    """The exact-arithmetic fixtures (tests/golden) straight through the kernels."""
+    with open(os.path.join(GOLD, "kat_f32.json")) as f:
+        k = json.load(f)
+    a = np.array(k["add"], dtype=np.uint64)
+    got = run_op(L, "add", "f32", a[:, 0].astype(np.uint32), a[:, 1].astype(np.uint32))
+    np.testing.assert_array_equal(got, a[:, 2].astype(np.uint32))
+    t = np.array(k["triad"], dtype=np.uint64)
+    for sv in np.unique(t[:, 0]):
+        m = t[:, 0] == sv
+        got = run_op(L, "triad", "f32", t[m, 1].astype(np.uint32), t[m, 2].astype(np.uint32), O.f32_from_bits(int(sv)))
+        np.testing.assert_array_equal(got, t[m, 3].astype(np.uint32))      # fused result ...
+    assert (t[:, 3] != t[:, 4]).sum() >= 250                                  # ... which mul+add would miss
+    sc = np.array(k["scale"], dtype=np.uint64)
+    for sv in np.unique(sc[:, 0]):
+        m = sc[:, 0] == sv
+        got = run_op(L, "scale", "f32", sc[m, 1].astype(np.uint32), None, O.f32_from_bits(int(sv)))
+        np.testing.assert_array_equal(got, sc[m, 2].astype(np.uint32))
+    with open(os.path.join(GOLD, "kat_bf16.json")) as f:
+        kb = json.load(f)
+    a = np.array(kb["add"], dtype=np.uint64)
+    got = run_op(L, "add", "bf16", a[:, 0].astype(np.uint16), a[:, 1].astype(np.uint16))
+    np.testing.assert_array_equal(got, a[:, 2].astype(np.uint16))
+    t = np.array(kb["triad"], dtype=np.uint64)
+    for sv in np.unique(t[:, 0]):
+        m = t[:, 0] == sv
+        got = run_op(L, "triad", "bf16", t[m, 1].astype(np.uint16), t[m, 2].astype(np.uint16), O.f32_from_bits(int(sv)))
+        np.testing.assert_array_equal(got, t[m, 3].astype(np.uint16))
+    sc = np.array(kb["scale"], dtype=np.uint64)
+    for sv in np.unique(sc[:, 0]):
+        m = sc[:, 0] == sv
+        got = run_op(L, "scale", "bf16", sc[m, 1].astype(np.uint16), None, O.f32_from_bits(int(sv)))
+        np.testing.assert_array_equal(got, sc[m, 2].astype(np.uint16))
+    # bf16 RNE alone: scale by 1.0 cannot be used (inputs are already bf16), so round through
+    # add with +0: widen(hi) + widen(lo-part) is not expressible either -> covered by add/triad above.
+
+
+def test_argument_errors_on_device(L):
+    buf = pkg.DeviceBuffer(1 << 20)
+    p = buf.ptr
+    vp = C.c_void_p
+    assert L.b200v_add_f32(vp(p), vp(p), vp(p + 4096), 256, None) == pkg.ERR_INVALID          # dst == a
+    assert b"overlap" in L.b200v_last_error()
+    assert L.b200v_triad_f32(vp(p + 512), 3.0, vp(p), vp(p + 8192), 256, None) == pkg.ERR_INVALID  # partial overlap
+    assert L.b200v_add_f32(vp(p + 2), vp(p + 4096), vp(p + 8192), 16, None) == pkg.ERR_ALIGN
+    assert L.b200v_add_bf16(vp(p + 1), vp(p + 4096), vp(p + 8192), 16, None) == pkg.ERR_ALIGN
+    assert L.b200v_add_f32(vp(p), vp(p + 4096), None, 16, None) == pkg.ERR_INVALID
+    assert L.b200v_copy_f32(vp(p), vp(p + 4096), 0, None) == pkg.OK                              # empty is fine
+    ws = pkg.DeviceBuffer(64)
+    assert L.b200v_checksum(vp(p), 1024, 0, vp(ws.ptr), 64, vp(p + 4096), None) == pkg.ERR_INVALID
+    assert b"workspace" in L.b200v_last_error()
+    pkg.check(L.b200v_device_sync())
+    buf.free()
+    ws.free()
+
+
+@pytest.mark.parametrize("nbytes,off", [(0, 0), (1, 0), (3, 0), (4, 0), (17, 4), (4096, 0), (4099, 8), (1_000_003, 12),
+                                        ((64 << 20) + 6, 4)])
+def test_checksum_matches_oracle(L, nbytes, off):
+    rng = np.random.default_rng(nbytes + off)
+    host = rng.integers(0, 256, size=nbytes, dtype=np.uint8)
+    buf = pkg.DeviceBuffer(nbytes + off + 16).upload(host, off) if nbytes else pkg.DeviceBuffer(64)
+    for word_offset in (0, (1 << 32) - 3, 123456789012):
+        assert pkg.checksum(buf.at(off), nbytes, word_offset) == O.checksum(host, word_offset)
+    buf.free()
+
+
+def test_checksum_workspace_reuse_and_shards(L):
+    n = 3_000_001
+    x = O.fill("f32", 0, n, SEED, 4, O.GEN_BITS)
+    buf = pkg.DeviceBuffer(n * 4).upload(x)
+    ws = pkg.DeviceBuffer(L.b200v_checksum_workspace_bytes())
+    pkg.check(L.b200v_memset(C.c_void_p(ws.ptr), 0xFF, ws.nbytes, None))      # dirty scratch must not matter
+    whole = pkg.checksum(buf.at(0), n * 4, 0, ws)
+    assert whole == O.checksum(x)
+    assert pkg.checksum(buf.at(0), n * 4, 0, ws) == whole                       # second use of the same scratch
+    total = [0, 0]
+    for r in range(3):
+        b, c = pkg.shard_range(n, r, 3)
+        s = pkg.checksum(buf.at(4 * b), 4 * c, b, ws)
+        total = [(total[0] + s[0]) & M64, (total[1] + s[1]) & M64]
+    assert tuple(total) == whole
+    buf.free()
+    ws.free()
+
+
+@pytest.mark.parametrize("pinned", [True, False])
+def test_vector_add_host_buffers(L, pinned):
+    """The cuda-samples call shape: host arrays in, host array out, H2D/D2H inside the call."""
+    for n in (50_000, 1, (8 << 20), (20 << 20) + 77):
+        a = O.fill("f32", 0, n, SEED, 0, O.GEN_UNIT)
+        b = O.fill("f32", 0, n, SEED, 1, O.GEN_UNIT)
+        want = O.op("add", "f32", n, x=a, y=b)
+        if pinned:
+            bufs = [pkg.PinnedBuffer(n * 4) for _ in range(3)]
+            ha, hb, hc = (x.view(np.uint32) for x in bufs)
+            ha[:] = a
+            hb[:] = b
+        else:
+            ha, hb, hc = a.copy(), b.copy(), np.zeros(n, dtype=np.uint32)
+        hc[:] = 0
+        vp = lambda arr: arr.ctypes.data_as(C.c_void_p)
+        pkg.check(L.b200v_vector_add_host(vp(ha), vp(hb), vp(hc), n))
+        np.testing.assert_array_equal(np.asarray(hc), want)
+        pkg.check(L.b200v_vector_add_host(vp(ha), vp(hb), vp(hc), n))          # staging buffers are reused
+        np.testing.assert_array_equal(np.asarray(hc), want)
+        del ha, hb, hc
+        if pinned:
+            for x in bufs:
+                x.free()
+    pkg.check(L.b200v_vector_add_host_release())
+
+
+# ------------------------------------------------------------------------------------------------
+# BASELINE.json sizes: verified through the checksum property (shards of the host oracle's output
+# add up to the device's checksum) plus bit-exact windows brought back to the host.
+
+def oracle_checksum_chunked(op, dtype, n, start, s, mode=O.GEN_UNIT, chunk=1 << 24):
+    tot = [0, 0]
+    for off in range(0, n, chunk):
+        m = min(chunk, n - off)
+        x = O.fill(dtype, start + off, m, SEED, 0, mode)
+        y = O.fill(dtype, start + off, m, SEED, 1, mode)
+        out = O.op(op, dtype, m, s=s, x=x, y=y, threads=0)
+        per_word = 1 if dtype == "f32" else 2
+        assert off % per_word == 0
+        c = O.checksum(out, off // per_word, threads=0)
+        tot = [(tot[0] + c[0]) & M64, (tot[1] + c[1]) & M64]
+    return tuple(tot)
+
+
+@pytest.mark.parametrize("op,dtype,log2n", [("add", "f32", 28), ("triad", "f32", 28), ("triad", "bf16", 28),
+                                            ("copy", "f32", 28), ("scale", "bf16", 27)])
+def test_baseline_size_checksum_and_windows(L, op, dtype, log2n):
+    n = (1 << log2n)
+    e = esz(dtype)
+    start = (1 << 32) - (1 << 20)            # global indices cross the 2^32 boundary
+    dx, dy, dd = (pkg.DeviceBuffer(n * e) for _ in range(3))
+    pkg.check(L.b200v_fill(pkg.DTYPES[dtype], C.c_void_p(dx.ptr), start, n, SEED, 0, O.GEN_UNIT, None))
+    pkg.check(L.b200v_fill(pkg.DTYPES[dtype], C.c_void_p(dy.ptr), start, n, SEED, 1, O.GEN_UNIT, None))
+    pkg.stream_op(op, dtype, C.c_void_p(dd.ptr), C.c_void_p(dx.ptr), C.c_void_p(dy.ptr), 3.0, n)
+    got = pkg.checksum(C.c_void_p(dd.ptr), n * e, 0)
+    assert got == oracle_checksum_chunked(op, dtype, n, start, 3.0)
+    for woff in (0, n // 3 + 1, n - 65_536):
+        m = 65_536
+        x = O.fill(dtype, start + woff, m, SEED, 0, O.GEN_UNIT)
+        y = O.fill(dtype, start + woff, m, SEED, 1, O.GEN_UNIT)
+        np.testing.assert_array_equal(dd.download(pkg.NP_BITS[dtype], m, woff * e), O.op(op, dtype, m, s=3.0, x=x, y=y))
+    for b in (dx, dy, dd):
+        b.free()
+
+
+def test_time_op_reports_device_times(L):
+    n = 1 << 26
+    dx, dy, dd = (pkg.DeviceBuffer(n * 4) for _ in range(3))
+    pkg.check(L.b200v_fill(pkg.F32, C.c_void_p(dx.ptr), 0, n, SEED, 0, O.GEN_UNIT, None))
+    pkg.check(L.b200v_fill(pkg.F32, C.c_void_p(dy.ptr), 0, n, SEED, 1, O.GEN_UNIT, None))
+    t = pkg.Timing()
+    t.struct_size = C.sizeof(pkg.Timing)
+    pkg.check(L.b200v_time_op(pkg.OP_TRIAD, pkg.F32, C.c_void_p(dd.ptr), C.c_void_p(dx.ptr), C.c_void_p(dy.ptr),
+                              3.0, n, 3, 10, None, C.byref(t)))
+    assert t.iters == 10 and t.bytes_per_launch == 12 * n
+    assert 0 < t.best_ms <= t.median_ms
+    gbs = t.bytes_per_launch / t.best_ms * 1e-6
+    assert 1000 < gbs < 12000, gbs           # an HBM3e part, and not a no-op
+    for b in (dx, dy, dd):
+        b.free()
