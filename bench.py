@@ -41,7 +41,17 @@ BYTES_PER_STEP = 12 * N_ELEMS          # 12 B per fp32 element
 NOMINAL_GBS = 8000.0
 FALLBACK_GBS = 6650.0                  # B200_PROFILING.md fallback when MEASURED_PEAKS.json is absent
 SEED = 20261106
-CPU_SAMPLE_LOG2 = 26                   # elements per CPU step in the reference arm / cpu_baseline
+def _cpu_sample_log2():
+    """Elements per CPU step in the reference arm / cpu_baseline: the full 2^28 workload (3 GiB of
+    arrays, larger than any host L3, like the GPU's) when host RAM allows, else 2^26."""
+    try:
+        import psutil
+        return 28 if psutil.virtual_memory().available > (16 << 30) else 26
+    except Exception:
+        return 26
+
+
+CPU_SAMPLE_LOG2 = _cpu_sample_log2()
 
 
 def measured_peak():
@@ -161,7 +171,7 @@ def cpu_baseline(budget_s=10.0):
         step()
         reps += 1
         dt = time.perf_counter() - t0
-        if dt >= budget_s or reps >= 400:
+        if dt >= budget_s or reps >= 20000:
             break
     gbs = 12.0 * n * reps / dt * 1e-9
     return {"value": round(gbs, 2), "unit": "GB/s", "cores": cores, "kind": "port",
@@ -182,7 +192,7 @@ def run_reference(args, rank):
     dt = time.perf_counter() - t0
     gbs = 12.0 * n * args.steps / dt * 1e-9
     sample = (f"each step = oracle_add_f32 (OpenMP, {cores} threads) over N=2^{CPU_SAMPLE_LOG2} fp32 elements resident in "
-              f"host RAM, a bounded sample of the 2^{LOG2_N} workload; GB/s is size-independent for a streaming loop")
+              f"host RAM, {'the full' if CPU_SAMPLE_LOG2 == LOG2_N else 'a bounded sample of the'} 2^{LOG2_N} workload")
     line = {
         "impl": "reference", "metric": METRIC, "value": round(gbs, 2), "unit": "GB/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(dt / args.steps * 1e3, 4),
@@ -203,52 +213,48 @@ def main():
     ap.add_argument("--steps", type=int, default=1000)
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="vectoradd", choices=["vectoradd", "triad-sharded"],
+                    help="vectoradd: configs[1], 2^28 fp32 per GPU (weak, the default and the graded line); "
+                         "triad-sharded: configs[3], 2^32 fp32 in total split over the ranks (strong)")
     ap.add_argument("--e2e-steps", type=int, default=8)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
 
-    rank = int(os.environ.get("RANK", "0"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-
     if args.impl == "reference":
-        run_reference(args, rank)
+        run_reference(args, int(os.environ.get("RANK", "0")))
         return 0
 
+    import numpy as np
+    import oracle_lib as O
     pkg = importlib.import_module("kubernetes-with-nvidia-gpu_b200")
+    ranks_mod = importlib.import_module("kubernetes-with-nvidia-gpu_b200.ranks")
     L = pkg.lib()          # raises if libb200v.so is missing: no fallback
+    R = ranks_mod.Ranks(backend="nccl" if int(os.environ.get("WORLD_SIZE", "1")) > 1 else None,
+                        device_sync=lambda: pkg.check(L.b200v_device_sync()))
+    rank, local_rank, world = R.rank, R.local_rank, R.world
     pkg.check(L.b200v_set_device(local_rank))
     pkg.check(L.b200v_require_sm100(local_rank))
     info = pkg.device_info(local_rank)
 
-    dist = None
-    if world > 1:
-        import torch
-        import torch.distributed as dist
-        torch.cuda.set_device(local_rank)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-
-    def barrier():
-        if dist is not None:
-            dist.barrier()
-        pkg.check(L.b200v_device_sync())
-
-    def max_over_ranks(ms):
-        if dist is None:
-            return ms
-        import torch
-        t = torch.tensor([ms], dtype=torch.float64, device=f"cuda:{local_rank}")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
+    sharded = args.workload == "triad-sharded"
+    if sharded:
+        total = 1 << 32
+        start, n_local = pkg.shard_range(total, rank, world)
+        main_op, main_name = pkg.OP_TRIAD, "triad"
+    else:
+        n_local = N_ELEMS
+        start = rank * N_ELEMS          # rank r owns [r*N, (r+1)*N) of the job's global index space
+        total = world * N_ELEMS
+        main_op, main_name = pkg.OP_ADD, "add"
+    bytes_local = 12 * n_local
+    bytes_job = 12 * total
 
     vp = C.c_void_p
-    nbytes = 4 * N_ELEMS
+    nbytes = 4 * n_local
     dA, dB, dC = (pkg.DeviceBuffer(nbytes) for _ in range(3))
-    # each rank owns the shard [rank*N, (rank+1)*N) of the job's global index space
-    start = rank * N_ELEMS
-    pkg.check(L.b200v_fill(pkg.F32, vp(dA.ptr), start, N_ELEMS, SEED, 0, pkg.GEN_UNIT, None))
-    pkg.check(L.b200v_fill(pkg.F32, vp(dB.ptr), start, N_ELEMS, SEED, 1, pkg.GEN_UNIT, None))
+    pkg.check(L.b200v_fill(pkg.F32, vp(dA.ptr), start, n_local, SEED, 0, pkg.GEN_UNIT, None))
+    pkg.check(L.b200v_fill(pkg.F32, vp(dB.ptr), start, n_local, SEED, 1, pkg.GEN_UNIT, None))
     stream = vp(None)
     pkg.check(L.b200v_stream_create(C.byref(stream)))
     ev0, ev1 = vp(None), vp(None)
@@ -259,69 +265,73 @@ def main():
     sampler.start()
 
     def timed(fn, steps):
-        barrier()
+        R.barrier()
         pkg.check(L.b200v_event_record(ev0, stream))
         for _ in range(steps):
             fn()
         pkg.check(L.b200v_event_record(ev1, stream))
         pkg.check(L.b200v_event_sync(ev1))
-        barrier()
+        R.barrier()
         ms = C.c_float(0)
         pkg.check(L.b200v_event_elapsed_ms(ev0, ev1, C.byref(ms)))
         return ms.value
 
-    add = lambda: pkg.check(L.b200v_add_f32(vp(dC.ptr), vp(dA.ptr), vp(dB.ptr), N_ELEMS, stream))
-    triad = lambda: pkg.check(L.b200v_triad_f32(vp(dC.ptr), 3.0, vp(dA.ptr), vp(dB.ptr), N_ELEMS, stream))
+    add = lambda: pkg.check(L.b200v_add_f32(vp(dC.ptr), vp(dA.ptr), vp(dB.ptr), n_local, stream))
+    triad = lambda: pkg.check(L.b200v_triad_f32(vp(dC.ptr), 3.0, vp(dA.ptr), vp(dB.ptr), n_local, stream))
+    main_fn, other_fn = (triad, add) if sharded else (add, triad)
 
     # ---- device-resident leg (value): W warm-up steps, then exactly K timed steps ----
     sampler.mark("load_start")
     for _ in range(args.warmup):
-        add()
+        main_fn()
     sampler.mark("timed_start")
-    ms_local = timed(add, args.steps)
+    ms_local = timed(main_fn, args.steps)
     sampler.mark("timed_end")
-    ms_total = max_over_ranks(ms_local)
+    ms_total = R.max(ms_local)
     ms_per_step = ms_total / args.steps
-    value = world * BYTES_PER_STEP / ms_per_step * 1e-6
+    value = bytes_job / ms_per_step * 1e-6
 
-    # the north-star kernel (triad, same 12 B/element) as a second, separately timed line
-    for _ in range(args.warmup):
-        triad()
-    triad_steps = max(min(args.steps, 200), 3)
-    triad_ms = max_over_ranks(timed(triad, triad_steps)) / triad_steps
-    sampler.mark("load_end")
-    triad_gbs_per_gpu = BYTES_PER_STEP / triad_ms * 1e-6
-
-    # cheap in-run parity check of what was just timed: device checksum vs the oracle on a window
-    import numpy as np
-    import oracle_lib as O
-    add()
-    pkg.check(L.b200v_stream_sync(stream))
+    # in-run parity of what was just timed: whole-output device checksum (summed over ranks) against
+    # the host oracle on bounded windows, plus a bit-exact window brought back to the host
     w = 1 << 16
-    got = dC.download(np.uint32, w, 4 * (N_ELEMS - w))
-    want = O.op("add", "f32", w, x=O.fill("f32", start + N_ELEMS - w, w, SEED, 0), y=O.fill("f32", start + N_ELEMS - w, w, SEED, 1))
-    parity_ok = bool((got == want).all())
+    got = dC.download(np.uint32, w, 4 * (n_local - w))
+    gx = O.fill("f32", start + n_local - w, w, SEED, 0)
+    gy = O.fill("f32", start + n_local - w, w, SEED, 1)
+    want = O.op(main_name, "f32", w, s=3.0, x=gx, y=gy)
+    parity_ok = R.all_ok(bool((got == want).all()))
+    job_checksum = R.sum_checksums(pkg.checksum(vp(dC.ptr), nbytes, start))
+
+    # the other 12 B/element kernel as a second, separately timed line (triad is the north-star kernel)
+    for _ in range(args.warmup):
+        other_fn()
+    other_steps = max(min(args.steps, 200), 3)
+    other_ms = R.max(timed(other_fn, other_steps)) / other_steps
+    sampler.mark("load_end")
+    other_gbs = bytes_job / other_ms * 1e-6
 
     # ---- end-to-end leg: host buffers through the public call, copies inside the timed region ----
     for b in (dA, dB, dC):
         b.free()
-    hA, hB, hC = (pkg.PinnedBuffer(nbytes) for _ in range(3))
+    n_e2e = N_ELEMS
+    e2e_bytes = 4 * n_e2e
+    hA, hB, hC = (pkg.PinnedBuffer(e2e_bytes) for _ in range(3))
     va, vb, vc = (h.view(np.uint32) for h in (hA, hB, hC))
-    O.lib().oracle_fill_f32(vp(hA.ptr), start, N_ELEMS, SEED, 0, O.GEN_UNIT)
-    O.lib().oracle_fill_f32(vp(hB.ptr), start, N_ELEMS, SEED, 1, O.GEN_UNIT)
-    e2e_call = lambda: pkg.check(L.b200v_vector_add_host(vp(hA.ptr), vp(hB.ptr), vp(hC.ptr), N_ELEMS))
+    O.lib().oracle_fill_f32(vp(hA.ptr), start, n_e2e, SEED, 0, O.GEN_UNIT)
+    O.lib().oracle_fill_f32(vp(hB.ptr), start, n_e2e, SEED, 1, O.GEN_UNIT)
+    e2e_call = lambda: pkg.check(L.b200v_vector_add_host(vp(hA.ptr), vp(hB.ptr), vp(hC.ptr), n_e2e))
     e2e_call()   # warm-up: allocates the staging buffers
     e2e_call()
-    barrier()
+    R.barrier()
     t0 = time.perf_counter()
     for _ in range(args.e2e_steps):
         e2e_call()     # synchronous: returns when hC is complete in host memory
     e2e_ms_local = (time.perf_counter() - t0) * 1e3
-    barrier()
-    e2e_ms = max_over_ranks(e2e_ms_local) / args.e2e_steps
-    e2e_value = world * BYTES_PER_STEP / e2e_ms * 1e-6
-    w0 = N_ELEMS // 2
-    e2e_ok = bool((vc[w0:w0 + w] == O.op("add", "f32", w, x=np.ascontiguousarray(va[w0:w0 + w]), y=np.ascontiguousarray(vb[w0:w0 + w]))).all())
+    R.barrier()
+    e2e_ms = R.max(e2e_ms_local) / args.e2e_steps
+    e2e_value = world * 12 * n_e2e / e2e_ms * 1e-6
+    w0 = n_e2e // 2
+    e2e_ok = R.all_ok(bool((vc[w0:w0 + w] == O.op("add", "f32", w, x=np.ascontiguousarray(va[w0:w0 + w]),
+                                                     y=np.ascontiguousarray(vb[w0:w0 + w]))).all()))
     pkg.check(L.b200v_vector_add_host_release())
     del va, vb, vc
     for h in (hA, hB, hC):
@@ -329,49 +339,50 @@ def main():
 
     sampler.stop_flag = True
     sampler.join(timeout=2)
-
-    if dist is not None:
-        dist.barrier()
+    R.barrier()
     if rank != 0:
-        if dist is not None:
-            dist.destroy_process_group()
+        R.close()
         return 0
 
     peak, peak_src = measured_peak()
-    achieved = BYTES_PER_STEP / (ms_local / args.steps) * 1e-6     # rank 0's add kernel, GB/s
+    achieved = bytes_local / (ms_local / args.steps) * 1e-6     # rank 0's kernel, GB/s
+    other_name = "add" if sharded else "triad"
     line = {
         "metric": METRIC, "value": round(value, 1), "unit": "GB/s", "n_gpus": world, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": round(ms_per_step, 5), "higher_is_better": True, "scaling": "weak",
+        "warmup": args.warmup, "ms_per_step": round(ms_per_step, 5), "higher_is_better": True,
+        "scaling": "strong" if sharded else "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {
-            "workload": f"vectorAdd fp32 C=A+B, N=2^{LOG2_N} elements per GPU (BASELINE.json configs[1]), one kernel launch per step",
-            "bytes_per_step_per_gpu": BYTES_PER_STEP, "bytes_per_element": 12, "parallelism": f"shard{world} (no collective)",
-            "l2": "inputs are 3 GiB per GPU, far larger than the 126 MB L2: no flush between steps",
+            "workload": ("triad fp32 a=fma(s,c,b), 2^32 elements in total sharded over the ranks (BASELINE.json configs[3])" if sharded else
+                         f"vectorAdd fp32 C=A+B, N=2^{LOG2_N} elements per GPU (BASELINE.json configs[1])") + ", one kernel launch per step",
+            "elements_per_gpu": n_local, "bytes_per_step_per_gpu": bytes_local, "bytes_per_element": 12,
+            "parallelism": f"shard{world} (one process per GPU, no collective on the data path)",
+            "l2": f"the three arrays are {3 * nbytes >> 20} MiB per GPU, far larger than the 126 MB L2: no flush between steps",
             "gpu": info.name.decode(), "sm_count": info.sm_count,
         },
         "roofline": {
             "bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
-            "frac": round(achieved / peak, 4), "traffic": ncu_traffic_per_launch(),
-            "peak_source": peak_src, "kernel": "b200v::stream_kernel<OP_ADD,f32> via b200v_add_f32",
-            "algorithmic_bytes_per_launch": BYTES_PER_STEP,
+            "frac": round(achieved / peak, 4), "traffic": None if sharded else ncu_traffic_per_launch(),
+            "peak_source": peak_src, "kernel": f"b200v::stream_kernel<{main_name}, f32, 256-bit> via b200v_{main_name}_f32",
+            "algorithmic_bytes_per_launch": bytes_local,
             "frac_of_nominal_8000": round(achieved / NOMINAL_GBS, 4),
         },
-        "triad": {"gbs_per_gpu": round(triad_gbs_per_gpu, 1), "ms_per_step": round(triad_ms, 5), "steps": triad_steps,
-                  "frac_of_measured": round(triad_gbs_per_gpu / peak, 4),
-                  "frac_of_nominal_8000": round(triad_gbs_per_gpu / NOMINAL_GBS, 4),
-                  "node_gbs": round(world * triad_gbs_per_gpu, 1)},
-        "e2e": {"value": round(e2e_value, 2), "unit": "GB/s", "h2d_bytes_per_step": 8 * N_ELEMS * world,
-                "d2h_bytes_per_step": 4 * N_ELEMS * world, "ms_per_step": round(e2e_ms, 3), "steps": args.e2e_steps,
-                "api": "b200v_vector_add_host(hA, hB, hC, n) with pinned host buffers; host wall clock around the synchronous call"},
+        other_name: {"node_gbs": round(other_gbs, 1), "gbs_per_gpu": round(other_gbs / world, 1), "ms_per_step": round(other_ms, 5),
+                     "steps": other_steps, "frac_of_measured": round(other_gbs / world / peak, 4),
+                     "frac_of_nominal_8000": round(other_gbs / world / NOMINAL_GBS, 4)},
+        "e2e": {"value": round(e2e_value, 2), "unit": "GB/s", "h2d_bytes_per_step": 8 * n_e2e * world,
+                "d2h_bytes_per_step": 4 * n_e2e * world, "ms_per_step": round(e2e_ms, 3), "steps": args.e2e_steps,
+                "api": f"b200v_vector_add_host(hA, hB, hC, 2^{LOG2_N}) per rank with pinned host buffers; host wall clock around "
+                       "the synchronous call, max over ranks; bound by PCIe (2 GiB in + 1 GiB out per step per GPU)"},
         "gpu_launches": args.steps * world, "gpu_launches_per_rank": args.steps,
-        "parity": {"device_window_bit_exact": parity_ok, "e2e_window_bit_exact": e2e_ok},
+        "parity": {"device_window_bit_exact": parity_ok, "e2e_window_bit_exact": e2e_ok,
+                   "job_checksum": ["%016x" % job_checksum[0], "%016x" % job_checksum[1]]},
         "clocks": sampler.summary(),
     }
     if not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline()
     print(json.dumps(line), flush=True)
-    if dist is not None:
-        dist.destroy_process_group()
+    R.close()
     return 0 if (parity_ok and e2e_ok) else 1
 
 

@@ -1,0 +1,176 @@
+"""GPU tier: the pod entrypoint (gpu-validate) end to end — verdict line, exit code, every mode.
+Multi-GPU cases skip themselves on a one-GPU box (run them with `gpurun --gpus 2`)."""
+import json
+import os
+import re
+import subprocess
+
+import pytest
+
+from b200v_pkg import pkg
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def exe():
+    assert os.path.exists(pkg.LAUNCHER_PATH), "gpu-validate has not been built"
+    return pkg.LAUNCHER_PATH
+
+
+def run(exe, *args, timeout=600):
+    return subprocess.run([exe, *args], capture_output=True, text=True, timeout=timeout)
+
+
+def last_line(r):
+    return r.stdout.strip().splitlines()[-1]
+
+
+def ngpus():
+    return pkg.device_count()
+
+
+def test_default_pod_run(exe):
+    """No arguments = the Step 9 contract: GPU listed, vectorAdd N=50,000 verified, Test PASSED, exit 0."""
+    r = run(exe)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert last_line(r) == "Test PASSED"
+    assert "NVIDIA B200" in r.stdout and "sm_100" in r.stdout
+    assert "50000 of 50000 elements bit-identical" in r.stdout
+
+
+def test_fault_injection_fails_the_pod(exe):
+    r = run(exe, "--inject-fault")
+    assert r.returncode == 1
+    assert last_line(r) == "Test FAILED" and "Test PASSED" not in r.stdout
+    assert "verification failed at element 25000" in r.stdout
+
+
+@pytest.mark.parametrize("n", ["1", "3", "1000003", "268435456"])
+def test_smoke_sizes(exe, n):
+    r = run(exe, "--n", n)
+    assert r.returncode == 0 and last_line(r) == "Test PASSED", r.stdout + r.stderr
+
+
+def test_missing_device_index(exe):
+    r = run(exe, "--device", "64")
+    assert r.returncode == 2 and last_line(r) == "Test FAILED"
+
+
+def test_list_mode(exe):
+    r = run(exe, "--mode", "list")
+    assert r.returncode == 0
+    assert re.search(r"GPU 0: NVIDIA B200 .* 148 SMs", r.stdout)
+    assert "GPU-" in r.stdout and "driver API" in r.stdout
+
+
+def test_bench_mode_small_sweep(exe, tmp_path):
+    js = tmp_path / "bench.json"
+    r = run(exe, "--mode", "bench", "--min-log2-bytes", "20", "--max-log2-bytes", "28", "--iters", "5", "--json", str(js))
+    assert r.returncode == 0 and last_line(r) == "Test PASSED", r.stdout[-3000:] + r.stderr
+    d = json.load(open(js))
+    rows = d["rows"]
+    assert len(rows) == 2 * 9 * 4 and all(x["verified"] for x in rows)
+    assert any(x["cache_resident"] for x in rows) and not all(x["cache_resident"] for x in rows)
+    big = [x for x in rows if x["bytes_per_array"] == 1 << 28 and x["op"] == "triad"]
+    assert all(x["gbs"] > 4000 for x in big), big
+    assert d["cpu_threads"] >= 1 and len(d["cpu_rows"]) == 4
+
+
+def test_node_mode_one_gpu(exe, tmp_path):
+    js = tmp_path / "node.json"
+    r = run(exe, "--mode", "node", "--gpus", "1", "--log2n", "28", "--iters", "5", "--json", str(js))
+    assert r.returncode == 0 and last_line(r) == "Test PASSED", r.stdout + r.stderr
+    d = json.load(open(js))
+    assert d["ok"] and d["gpus"] == 1 and d["elements"] == 1 << 28 and d["node_gbs"] > 4000
+
+
+def test_node_mode_fault_injection(exe):
+    r = run(exe, "--mode", "node", "--gpus", "1", "--log2n", "24", "--iters", "2", "--inject-fault")
+    assert r.returncode == 1 and last_line(r) == "Test FAILED"
+
+
+def test_burnin_mode_verifies_every_pass(exe, tmp_path):
+    js = tmp_path / "burn.json"
+    r = run(exe, "--mode", "burnin", "--gpus", "1", "--log2n", "26", "--seconds", "2", "--json", str(js))
+    assert r.returncode == 0 and last_line(r) == "Test PASSED", r.stdout + r.stderr
+    d = json.load(open(js))
+    assert d["ok"] and d["ranks"][0]["passes"] >= 20
+
+
+def test_too_many_gpus_requested(exe):
+    r = run(exe, "--mode", "node", "--gpus", str(ngpus() + 1), "--log2n", "20")
+    assert r.returncode == 2 and last_line(r) == "Test FAILED"
+
+
+def test_p2p_single_gpu_is_a_pass(exe):
+    r = run(exe, "--mode", "p2p", "--gpus", "1")
+    assert r.returncode == 0 and last_line(r) == "Test PASSED"
+
+
+# ---- two or more GPUs -----------------------------------------------------------------------
+multi = pytest.mark.skipif("ngpus() < 2", reason="needs >= 2 GPUs")
+
+
+@multi
+def test_node_mode_sharded_over_all_gpus(exe, tmp_path):
+    g = ngpus()
+    js = tmp_path / "node.json"
+    r = run(exe, "--mode", "node", "--log2n", "30", "--iters", "5", "--json", str(js))
+    assert r.returncode == 0 and last_line(r) == "Test PASSED", r.stdout + r.stderr
+    d = json.load(open(js))
+    assert d["gpus"] == g and d["elements"] == 1 << 30 and len(d["ranks"]) == g
+    assert all(x["ok"] == 1 for x in d["ranks"])
+    assert d["node_gbs"] > 4000 * g * 0.8
+
+
+@multi
+def test_p2p_all_pairs(exe, tmp_path):
+    g = ngpus()
+    js = tmp_path / "p2p.json"
+    r = run(exe, "--mode", "p2p", "--p2p-bytes", str(256 << 20), "--iters", "8", "--json", str(js))
+    assert r.returncode == 0 and last_line(r) == "Test PASSED", r.stdout + r.stderr
+    d = json.load(open(js))
+    assert d["ok"] and len(d["pairs"]) == g * (g - 1)
+    assert all(p["memcpy_peer_gbs"] > 100 and p["peer_load_gbs"] > 100 for p in d["pairs"]), d["pairs"]
+
+
+@multi
+def test_p2p_fault_injection(exe):
+    r = run(exe, "--mode", "p2p", "--p2p-bytes", str(64 << 20), "--iters", "4", "--inject-fault")
+    assert r.returncode == 1 and last_line(r) == "Test FAILED"
+
+
+@multi
+def test_peer_entry_points_through_the_abi():
+    import ctypes as C
+    import numpy as np
+    import oracle_lib as O
+    L = pkg.lib()
+    n = (8 << 20) + 13
+    pkg.check(L.b200v_set_device(0))
+    src = pkg.DeviceBuffer(4 * n)
+    pkg.check(L.b200v_fill(pkg.F32, C.c_void_p(src.ptr), 77, n, 5, 9, pkg.GEN_BITS, None))
+    pkg.check(L.b200v_device_sync())
+    pkg.check(L.b200v_peer_enable(0, 1))
+    pkg.check(L.b200v_peer_enable(1, 0))
+    pkg.check(L.b200v_peer_enable(1, 0))      # idempotent
+    pkg.check(L.b200v_set_device(1))
+    dst = pkg.DeviceBuffer(4 * n)
+    want = O.fill("f32", 77, n, 5, 9, O.GEN_BITS)
+    pkg.check(L.b200v_peer_copy(C.c_void_p(dst.ptr), 1, C.c_void_p(src.ptr), 0, 4 * n, None))
+    np.testing.assert_array_equal(dst.download(np.uint32, n), want)
+    pkg.check(L.b200v_memset(C.c_void_p(dst.ptr), 0, 4 * n, None))
+    pkg.check(L.b200v_peer_pull(C.c_void_p(dst.ptr), C.c_void_p(src.ptr), 4 * n, None))
+    np.testing.assert_array_equal(dst.download(np.uint32, n), want)
+    assert pkg.checksum(C.c_void_p(dst.ptr), 4 * n) == O.checksum(want)
+    dst.free()
+    pkg.check(L.b200v_set_device(0))
+    src.free()
+
+
+@multi
+def test_full_mode(exe):
+    r = run(exe, "--mode", "full", "--log2n", "26", "--seconds", "2", "--p2p-bytes", str(128 << 20), "--iters", "4")
+    assert r.returncode == 0 and last_line(r) == "Test PASSED", r.stdout + r.stderr
+    assert "burn-in" in r.stdout and "peer-to-peer" in r.stdout

@@ -1,0 +1,129 @@
+"""CPU tier: the pod entrypoint's contract where no GPU exists — verdict line, exit codes, the
+host reference loop (BASELINE.json configs[0]) cross-checked against the oracle, and the pod
+manifest's envelope against the reference's Step 9 manifest."""
+import os
+import re
+import subprocess
+
+import pytest
+import yaml
+
+import oracle_lib as O
+from b200v_pkg import pkg, ROOT
+
+SEED = 20261106
+
+
+@pytest.fixture(scope="module")
+def exe():
+    if not os.path.exists(pkg.LAUNCHER_PATH):
+        pkg.build()
+    return pkg.LAUNCHER_PATH
+
+
+def run(exe, *args, env=None):
+    e = dict(os.environ)
+    if env:
+        e.update(env)
+    return subprocess.run([exe, *args], capture_output=True, text=True, timeout=300, env=e)
+
+
+def last_line(r):
+    return r.stdout.strip().splitlines()[-1]
+
+
+def _gpu_visible():
+    try:
+        return pkg.device_count() > 0
+    except Exception:
+        return False
+
+
+no_gpu = pytest.mark.skipif(_gpu_visible(), reason="checks the no-GPU verdict")
+
+
+@no_gpu
+def test_default_mode_fails_loudly_without_gpu(exe):
+    """No device => Test FAILED and a non-zero exit (restartPolicy: OnFailure acts on it); never a CPU pass."""
+    r = run(exe)
+    assert r.returncode == 2
+    assert last_line(r) == "Test FAILED"
+    assert "Test PASSED" not in r.stdout
+    assert "no usable CUDA device" in r.stdout
+
+
+@no_gpu
+@pytest.mark.parametrize("mode", ["bench", "node", "p2p", "burnin", "full", "list"])
+def test_every_gpu_mode_fails_without_gpu(exe, mode):
+    r = run(exe, "--mode", mode, "--seconds", "1")
+    assert r.returncode != 0
+    assert "Test PASSED" not in r.stdout
+    assert last_line(r) == "Test FAILED"
+
+
+def test_usage_errors(exe):
+    for bad in (["--bogus"], ["--mode"], ["--dtype", "fp64"], ["--mode", "nonsense"], ["--iters", "0"]):
+        r = run(exe, *bad)
+        assert r.returncode == 64, bad
+        assert last_line(r) == "Test FAILED"
+
+
+@pytest.mark.parametrize("n", [50_000, 1, 65_537])
+def test_host_reference_matches_oracle(exe, n):
+    """configs[0]: the launcher's own host loop (hostcheck.cpp) and the oracle are written
+    separately from the same spec; their checksums over the same inputs must agree."""
+    r = run(exe, "--mode", "host-reference", "--n", str(n))
+    assert r.returncode == 0 and last_line(r) == "Test PASSED"
+    m = re.search(r"add_checksum=([0-9a-f]{16}):([0-9a-f]{16}) triad_checksum=([0-9a-f]{16}):([0-9a-f]{16})", r.stdout)
+    assert m
+    a = O.fill("f32", 0, n, SEED, 0)
+    b = O.fill("f32", 0, n, SEED, 1)
+    add = O.checksum(O.op("add", "f32", n, x=a, y=b))
+    triad = O.checksum(O.op("triad", "f32", n, s=3.0, x=a, y=b))
+    assert (int(m.group(1), 16), int(m.group(2), 16)) == add
+    assert (int(m.group(3), 16), int(m.group(4), 16)) == triad
+    assert "no GPU is used" in r.stdout
+
+
+def test_host_reference_fault_injection_turns_the_verdict(exe):
+    r = run(exe, "--mode", "host-reference", "--inject-fault")
+    assert r.returncode == 1 and last_line(r) == "Test FAILED"
+
+
+def test_launcher_is_self_contained(exe):
+    """The image only gets driver libraries from the container runtime: no libcudart, no oracle."""
+    ldd = subprocess.run(["ldd", exe], capture_output=True, text=True).stdout
+    assert "libcudart" not in ldd and "liboracle" not in ldd and "libstdc++" not in ldd and "libb200v" not in ldd
+    archs = set(re.findall(r"sm_\d+a?", subprocess.run(["cuobjdump", "-lelf", exe], capture_output=True, text=True).stdout))
+    assert archs == {"sm_100a"}
+
+
+def test_pod_manifest_keeps_the_reference_envelope():
+    """Same envelope as the reference's Step 9 pod (reference README.md:304-318); only image/command/args differ."""
+    deploy = os.path.join(ROOT, "kubernetes-with-nvidia-gpu_b200", "deploy")
+    pod = yaml.safe_load(open(os.path.join(deploy, "pod-cuda-vector-add.yaml")))
+    ref_readme = "/root/reference/README.md"
+    if os.path.exists(ref_readme):
+        text = open(ref_readme).read()
+        block = text[text.index("apiVersion: v1\nkind: Pod"):]
+        ref = yaml.safe_load(block[:block.index("EOF")])
+    else:  # the GPU box has no /root/reference: the same structure, written out
+        ref = {"apiVersion": "v1", "kind": "Pod", "metadata": {"name": "cuda-vector-add"},
+               "spec": {"restartPolicy": "OnFailure", "containers": [{
+                   "name": "cuda-vector-add", "image": "nvidia/cuda:12.1.0-base-ubuntu22.04",
+                   "command": ["/bin/sh", "-c"], "args": ["nvidia-smi"],
+                   "resources": {"limits": {"nvidia.com/gpu": 1}}}]}}
+
+    def envelope(p):
+        c = dict(p["spec"]["containers"][0])
+        for k in ("image", "command", "args"):
+            c.pop(k)
+        return {"apiVersion": p["apiVersion"], "kind": p["kind"], "metadata": p["metadata"],
+                "restartPolicy": p["spec"]["restartPolicy"], "n_containers": len(p["spec"]["containers"]), "container": c}
+
+    assert envelope(pod) == envelope(ref)
+    c = pod["spec"]["containers"][0]
+    assert c["command"] == ["/usr/local/bin/gpu-validate"] and c["args"] == []
+    job = yaml.safe_load(open(os.path.join(deploy, "job-node-validate.yaml")))
+    jc = job["spec"]["template"]["spec"]["containers"][0]
+    assert jc["resources"]["limits"]["nvidia.com/gpu"] == 8 and "--mode" in jc["args"]
