@@ -2,7 +2,7 @@
 // CSV table (one row per configuration).  The product's csrc/tuning.h is set from these tables
 // (kept under profiles/).  Not part of the product; builds against the same stream_kernels.cuh.
 //
-//   tools/tune [log2_n=28] [iters=10] [stage=all|shape|hint|ref]
+//   tools/tune [log2_n=28] [iters=10] [stage=all|shape|hint|tma|ref]
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
@@ -12,6 +12,7 @@
 #include <vector>
 
 #include "stream_kernels.cuh"
+#include "stream_tma.cuh"
 
 using namespace b200v;
 
@@ -24,9 +25,25 @@ using namespace b200v;
         }                                                                                       \
     } while (0)
 
+__global__ void count_mismatch(const uint32_t* a, const uint32_t* b, size_t n, unsigned long long* out)
+{
+    unsigned long long bad = 0;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+        bad += a[i] != b[i];
+    if (bad) atomicAdd(out, bad);
+}
+
+__global__ void init_values(float* p, size_t n, uint32_t salt)
+{
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+        p[i] = (float)((((uint32_t)i ^ salt) * 2654435761u) >> 8) * 0x1p-24f;
+}
+
 struct Config {
     std::string stage;
     int op, vecb, unroll, block, ldh, sth;
+    int smem = 0;          // > 0: TMA variant (vecb = tile KiB, unroll = stages); grid modes are CTAs per SM
+
     size_t tile_elems;
     std::function<void(unsigned, void*, const void*, const void*, float, size_t)> launch;
     int regs;
@@ -49,6 +66,43 @@ static void add_cfg(const char* stage)
         k<<<grid, BLOCK>>>(d, x, y, s, n);
     };
     g_cfg.push_back(c);
+}
+
+template <int OP, int TILE_BYTES, int STAGES, int BLOCK> static void add_tma(const char* stage)
+{
+    Config c;
+    c.stage = stage;
+    c.op = OP; c.vecb = TILE_BYTES / 1024; c.unroll = STAGES; c.block = BLOCK; c.ldh = -1; c.sth = -1;
+    c.tile_elems = TILE_BYTES / 4;
+    c.smem = STAGES * TILE_BYTES * (kReadsY<OP> ? 2 : 1);
+    auto k = stream_kernel_tma<OP, false, TILE_BYTES, STAGES, BLOCK>;
+    CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, c.smem));
+    cudaFuncAttributes fa;
+    CK(cudaFuncGetAttributes(&fa, k));
+    c.regs = fa.numRegs;
+    const int smem = c.smem;
+    c.launch = [k, smem](unsigned grid, void* d, const void* x, const void* y, float s, size_t n) {
+        k<<<grid, BLOCK, smem>>>(d, x, y, s, n / (TILE_BYTES / 4));
+    };
+    g_cfg.push_back(c);
+}
+
+template <int OP> static void add_tma_all(const char* stage)
+{
+    add_tma<OP, 8192, 2, 256>(stage);
+    add_tma<OP, 8192, 3, 256>(stage);
+    add_tma<OP, 8192, 4, 256>(stage);
+    add_tma<OP, 8192, 6, 256>(stage);
+    add_tma<OP, 16384, 2, 256>(stage);
+    add_tma<OP, 16384, 3, 256>(stage);
+    add_tma<OP, 16384, 4, 256>(stage);
+    add_tma<OP, 16384, 3, 512>(stage);
+    add_tma<OP, 16384, 4, 512>(stage);
+    add_tma<OP, 32768, 2, 512>(stage);
+    add_tma<OP, 32768, 3, 512>(stage);
+    add_tma<OP, 32768, 3, 1024>(stage);
+    add_tma<OP, 4096, 4, 128>(stage);
+    add_tma<OP, 4096, 8, 128>(stage);
 }
 
 template <int OP, int LDH, int STH> static void add_shapes(const char* stage)
@@ -105,8 +159,9 @@ int main(int argc, char** argv)
     CK(cudaMalloc(&a, n * 4));
     CK(cudaMalloc(&b, n * 4));
     CK(cudaMalloc(&c, n * 4));
-    CK(cudaMemset(a, 0x3c, n * 4));
-    CK(cudaMemset(b, 0x3d, n * 4));
+    init_values<<<2048, 256>>>(a, n, 0x1234567u);
+    init_values<<<2048, 256>>>(b, n, 0x89abcdeu);
+    CK(cudaDeviceSynchronize());
     CK(cudaMemset(c, 0, n * 4));
 
     const bool all = !strcmp(stage, "all");
@@ -126,6 +181,15 @@ int main(int argc, char** argv)
         add_hints<OP_COPY, 32, 4, 256>("hint");
         add_hints<OP_COPY, 32, 8, 256>("hint");
     }
+
+    if (all || !strcmp(stage, "tma")) {
+        add_tma_all<OP_ADD>("tma");
+        add_tma_all<OP_TRIAD>("tma");
+        add_tma_all<OP_COPY>("tma");
+    }
+    float* cref = nullptr;
+    unsigned long long* dbad = nullptr;
+    CK(cudaMalloc(&dbad, 8));
 
     cudaEvent_t e0, e1;
     CK(cudaEventCreate(&e0));
@@ -156,11 +220,28 @@ int main(int argc, char** argv)
     const int ctas_modes[] = {0, 1, 2, 4, 8};
     for (const Config& cf : g_cfg) {
         const double bytes = (cf.op == OP_COPY ? 8.0 : 12.0) * n;
+        if (cf.smem > 0) {   // correctness of the TMA variant against the register kernel, once per config
+            if (!cref) CK(cudaMalloc(&cref, n * 4));
+            CK(cudaMemset(c, 0, n * 4));
+            CK(cudaMemset(dbad, 0, 8));
+            cf.launch(sms, c, a, b, 3.0f, n);
+            if (cf.op == OP_ADD) stream_kernel<OP_ADD, false, 32, 4, 512, 0, 0><<<(unsigned)(n / 16384), 512>>>(cref, a, b, 3.0f, n);
+            else if (cf.op == OP_TRIAD) stream_kernel<OP_TRIAD, false, 32, 4, 512, 0, 0><<<(unsigned)(n / 16384), 512>>>(cref, a, b, 3.0f, n);
+            else stream_kernel<OP_COPY, false, 32, 4, 512, 0, 0><<<(unsigned)(n / 16384), 512>>>(cref, a, b, 3.0f, n);
+            count_mismatch<<<1024, 256>>>((const uint32_t*)c, (const uint32_t*)cref, n, dbad);
+            unsigned long long bad = 0;
+            CK(cudaMemcpy(&bad, dbad, 8, cudaMemcpyDeviceToHost));
+            if (bad) {
+                fprintf(stderr, "TMA variant tile=%dK stages=%d block=%d op=%d: %llu mismatches\n", cf.vecb, cf.unroll, cf.block, cf.op, bad);
+                return 3;
+            }
+        }
         for (int cps : ctas_modes) {
             size_t tiles = n / cf.tile_elems;
             size_t grid = tiles;
             if (cps > 0) grid = std::min(tiles, (size_t)sms * cps);
             if (cps * cf.block > 2048) continue;
+            if (cf.smem > 0 && (cps == 0 || (size_t)cps * (cf.smem + 1024) > 227 * 1024)) continue;
             for (int i = 0; i < 2; ++i) cf.launch((unsigned)grid, c, a, b, 3.0f, n);
             CK(cudaGetLastError());
             float best = 1e30f;
