@@ -155,6 +155,23 @@ B200V_API size_t b200v_checksum_workspace_bytes(void);
 B200V_API int b200v_checksum(const void *d_buf, size_t nbytes, uint64_t word_offset, void *d_workspace,
                    size_t workspace_bytes, uint64_t *d_out, void *stream);
 
+/* b200v_checksum_static has no counterpart in the reference (nor among the entry points above
+ * that mirror its pod): it is b200v_checksum for callers that cannot supply a workspace because
+ * they cannot allocate device memory when they need the checksum — a burn-in whose arrays already
+ * occupy all free HBM, a probe inside a process whose allocator has reserved the whole GPU, a
+ * hook that must avoid cudaMalloc/cudaFree because they synchronise the device.  The scratch is a
+ * fixed array inside the library image (about 16 KiB on every GPU that loads it); the call
+ * allocates nothing.  Results are identical to b200v_checksum.
+ *  - at most B200V_CHECKSUM_STATIC_MAX_BYTES per call, else B200V_ERR_INVALID (split the buffer:
+ *    pieces add up; or use b200v_checksum);
+ *  - the first call on each device also looks up the array's device address: make it at start-up,
+ *    with that device current, before any stream capture begins;
+ *  - all calls on a device share the array: calls that overlap on the GPU race, so keep them on
+ *    one stream or order them with events.                                                      */
+#define B200V_CHECKSUM_STATIC_MAX_BYTES (1ull << 32)
+B200V_API int b200v_checksum_static(const void *d_buf, size_t nbytes, uint64_t word_offset, uint64_t *d_out,
+                                    void *stream);
+
 /* ---- timing (device-timed only; no host clocks in reported GPU numbers) -------------------- */
 B200V_API int b200v_event_create(void **event);
 B200V_API int b200v_event_destroy(void *event);

@@ -108,6 +108,7 @@ def _signatures():
         "b200v_vector_add_host_release": (i32, []),
         "b200v_checksum_workspace_bytes": (sz, []),
         "b200v_checksum": (i32, [vp, sz, u64, vp, sz, vp, vp]),
+        "b200v_checksum_static": (i32, [vp, sz, u64, vp, vp]),
         "b200v_event_create": (i32, [pvp]),
         "b200v_event_destroy": (i32, [vp]),
         "b200v_event_record": (i32, [vp, vp]),

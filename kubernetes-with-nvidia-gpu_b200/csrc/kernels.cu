@@ -441,6 +441,84 @@ int b200v_checksum(const void* d_buf, size_t nbytes, uint64_t word_offset, void*
     return B200V_OK;
 }
 
+// ------------------------------------------------------------------------------------------
+// b200v_checksum_static: the checksum for callers that have no way to hand over scratch memory.
+//
+// Some users of this library cannot allocate device memory at the moment they want a checksum:
+// a burn-in that has deliberately filled every free byte of HBM with its arrays (a later
+// cudaMalloc simply fails), a liveness probe living inside a process whose framework allocator
+// has already reserved the whole GPU, or a monitoring hook that must not call cudaMalloc/cudaFree
+// because those calls synchronise the device and would stall the work it is watching.  For them
+// the reduction's scratch lives in the library image itself: the file-scope array below, present
+// on every GPU that loads libb200v (about 16 KiB per GPU, held until the process exits).
+//
+// Same kernel, same result as b200v_checksum; only the origin of the scratch differs.
+//  * Limit: buffers up to B200V_CHECKSUM_STATIC_MAX_BYTES (4 GiB).  The array has room for one
+//    partial pair per CTA for at most kStaticMaxBlocks CTAs, and the limit budgets 4 MiB of input
+//    per slot: since every caller on the device shares the array, one call should not keep it
+//    busy for long (4 GiB is about 0.6 ms of HBM reading).  Anything larger is refused with
+//    B200V_ERR_INVALID — checksum it in pieces (pieces add up, see b200v_checksum) or use
+//    b200v_checksum with your own workspace.
+//  * The FIRST call on each device resolves the array's device address (cudaGetSymbolAddress,
+//    with that device current), which may make the driver load the module.  Make that first call
+//    during start-up, before any stream capture is begun.
+//  * Every call on a device shares the one array and finds the previous call's partials in it.
+//    The arrival counter is cleared on the stream before each launch; the partials need no
+//    clearing (each CTA overwrites its own slot before the combine reads it).  Two calls that
+//    overlap on the GPU (different streams, no ordering between them) race on the array and
+//    give garbage: keep calls on one stream, or order them with events.
+//  * Nothing here calls cudaMalloc, cudaFree or any allocating library routine.
+
+constexpr int kStaticMaxBlocks = 1024;
+constexpr size_t kStaticHeaderBytes = 256;   // arrival counter, padded so the partials stay 256-byte aligned
+constexpr size_t kStaticScratchBytes = kStaticHeaderBytes + (size_t)kStaticMaxBlocks * 16;
+constexpr size_t kStaticBytesPerBlock = (size_t)4 << 20;
+static_assert((uint64_t)kStaticMaxBlocks * kStaticBytesPerBlock == B200V_CHECKSUM_STATIC_MAX_BYTES,
+              "the documented limit and the scratch array disagree");
+
+// In host code this name is only a handle for cudaGetSymbolAddress, never a device pointer.
+static __device__ __align__(256) unsigned char g_checksum_static_scratch[kStaticScratchBytes];
+
+// device address of the array, per device ordinal, resolved on first use
+static void* g_checksum_static_addr[64] = {};
+
+int b200v_checksum_static(const void* d_buf, size_t nbytes, uint64_t word_offset, uint64_t* d_out, void* stream)
+{
+    B200V_REQUIRE(d_out != nullptr, B200V_ERR_INVALID, "NULL output");
+    B200V_REQUIRE(d_buf || nbytes == 0, B200V_ERR_INVALID, "NULL buffer");
+    B200V_REQUIRE((uint64_t)nbytes <= B200V_CHECKSUM_STATIC_MAX_BYTES, B200V_ERR_INVALID,
+                  "b200v_checksum_static takes at most %llu bytes per call (got %zu): split the buffer or use "
+                  "b200v_checksum with a caller-owned workspace",
+                  (unsigned long long)B200V_CHECKSUM_STATIC_MAX_BYTES, nbytes);
+    B200V_REQUIRE((uintptr_t)d_out % 8 == 0, B200V_ERR_ALIGN, "output must be 8-byte aligned");
+    B200V_REQUIRE((uintptr_t)d_buf % 4 == 0, B200V_ERR_ALIGN, "buffer must be 4-byte aligned");
+    int sms = 0;
+    if (int rc = current_sm_count(&sms)) return rc;
+    int dev = 0;
+    B200V_CUDA(cudaGetDevice(&dev));
+    if (g_checksum_static_addr[dev] == nullptr) {   // once per device, with that device current
+        void* p = nullptr;
+        B200V_CUDA(cudaGetSymbolAddress(&p, g_checksum_static_scratch));
+        B200V_REQUIRE(p != nullptr, B200V_ERR_CUDA, "cudaGetSymbolAddress returned a NULL scratch address");
+        g_checksum_static_addr[dev] = p;
+    }
+    unsigned char* scratch = static_cast<unsigned char*>(g_checksum_static_addr[dev]);
+    unsigned int* counter = reinterpret_cast<unsigned int*>(scratch);
+    uint64_t* partials = reinterpret_cast<uint64_t*>(scratch + kStaticHeaderBytes);
+
+    cudaStream_t st = as_stream(stream);
+    size_t grid = (nbytes / 16 + kChecksumBlock * kChecksumUnroll - 1) / (kChecksumBlock * kChecksumUnroll);
+    size_t cap = (size_t)sms * 4;
+    if (cap > kStaticMaxBlocks) cap = kStaticMaxBlocks;
+    if (grid > cap) grid = cap;
+    if (grid == 0) grid = 1;
+    B200V_CUDA(cudaMemsetAsync(counter, 0, 16, st));   // the counter must start at zero; a memset allocates nothing
+    checksum_kernel<<<(unsigned)grid, kChecksumBlock, 0, st>>>(reinterpret_cast<const unsigned char*>(d_buf), nbytes,
+                                                              word_offset, counter, partials, d_out);
+    B200V_CUDA(cudaGetLastError());
+    return B200V_OK;
+}
+
 int b200v_peer_pull(void* d_local_dst, const void* d_peer_src, size_t bytes, void* stream)
 {
     B200V_REQUIRE(d_local_dst && d_peer_src, B200V_ERR_INVALID, "NULL pointer");
