@@ -144,6 +144,9 @@ B200V_API uint64_t b200v_op_bytes(int op, int dtype, size_t n);
  * PCIe speed; pageable ones work but are staged by the driver.  Synchronous.                */
 B200V_API int b200v_vector_add_host(const float *hA, const float *hB, float *hC, size_t n);
 B200V_API int b200v_vector_add_host_release(void);   /* frees the per-device staging buffers */
+/* pipeline shape: elements per staged chunk and number of chunk slots (streams) in flight;
+ * takes effect at the next b200v_vector_add_host call.  Defaults: 8 Mi elements, 3 slots.    */
+B200V_API int b200v_vector_add_host_config(size_t chunk_elems, int slots);
 
 /* ---- checksum (verifies outputs too large to bring back) -----------------------------------
  * Order-independent, position-sensitive checksum of a device buffer read as little-endian

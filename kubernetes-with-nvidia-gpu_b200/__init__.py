@@ -106,6 +106,7 @@ def _signatures():
         "b200v_op_bytes": (u64, [i32, i32, sz]),
         "b200v_vector_add_host": (i32, [vp, vp, vp, sz]),
         "b200v_vector_add_host_release": (i32, []),
+        "b200v_vector_add_host_config": (i32, [sz, i32]),
         "b200v_checksum_workspace_bytes": (sz, []),
         "b200v_checksum": (i32, [vp, sz, u64, vp, sz, vp, vp]),
         "b200v_checksum_static": (i32, [vp, sz, u64, vp, vp]),

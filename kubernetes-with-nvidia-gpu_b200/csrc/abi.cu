@@ -369,21 +369,25 @@ int b200v_shard_range(uint64_t n, int rank, int world, uint64_t* begin, uint64_t
 
 namespace {
 
-constexpr int kSlots = 3;
-constexpr size_t kChunkElems = (size_t)8 << 20;  // 8 Mi fp32 = 32 MiB per array per slot
+constexpr int kMaxSlots = 8;
+// defaults from the round-1 sweep (profiles/): see b200v_vector_add_host_config
+int g_slots = 3;
+size_t g_chunk_elems = (size_t)8 << 20;  // 8 Mi fp32 = 32 MiB per array per slot
 
 struct HostPipe {
     bool ready = false;
-    cudaStream_t stream[kSlots] = {};
-    float* a[kSlots] = {};
-    float* b[kSlots] = {};
-    float* c[kSlots] = {};
+    int slots = 0;
+    size_t chunk_elems = 0;
+    cudaStream_t stream[kMaxSlots] = {};
+    float* a[kMaxSlots] = {};
+    float* b[kMaxSlots] = {};
+    float* c[kMaxSlots] = {};
 };
 HostPipe g_pipe[64];
 
 int pipe_release(HostPipe& p)
 {
-    for (int i = 0; i < kSlots; ++i) {
+    for (int i = 0; i < kMaxSlots; ++i) {
         if (p.a[i]) cudaFree(p.a[i]);
         if (p.b[i]) cudaFree(p.b[i]);
         if (p.c[i]) cudaFree(p.c[i]);
@@ -398,12 +402,15 @@ int pipe_release(HostPipe& p)
 
 int pipe_init(HostPipe& p)
 {
-    if (p.ready) return B200V_OK;
-    for (int i = 0; i < kSlots; ++i) {
+    if (p.ready && p.slots == g_slots && p.chunk_elems == g_chunk_elems) return B200V_OK;
+    if (p.ready) pipe_release(p);
+    p.slots = g_slots;
+    p.chunk_elems = g_chunk_elems;
+    for (int i = 0; i < p.slots; ++i) {
         cudaError_t e = cudaStreamCreateWithFlags(&p.stream[i], cudaStreamNonBlocking);
-        if (e == cudaSuccess) e = cudaMalloc((void**)&p.a[i], kChunkElems * sizeof(float));
-        if (e == cudaSuccess) e = cudaMalloc((void**)&p.b[i], kChunkElems * sizeof(float));
-        if (e == cudaSuccess) e = cudaMalloc((void**)&p.c[i], kChunkElems * sizeof(float));
+        if (e == cudaSuccess) e = cudaMalloc((void**)&p.a[i], p.chunk_elems * sizeof(float));
+        if (e == cudaSuccess) e = cudaMalloc((void**)&p.b[i], p.chunk_elems * sizeof(float));
+        if (e == cudaSuccess) e = cudaMalloc((void**)&p.c[i], p.chunk_elems * sizeof(float));
         if (e != cudaSuccess) {
             pipe_release(p);
             return cuda_status(e, "staging buffers for b200v_vector_add_host", __FILE__, __LINE__);
@@ -414,6 +421,16 @@ int pipe_init(HostPipe& p)
 }
 
 }  // namespace
+
+int b200v_vector_add_host_config(size_t chunk_elems, int slots)
+{
+    B200V_REQUIRE(slots >= 1 && slots <= kMaxSlots, B200V_ERR_INVALID, "slots %d not in [1, %d]", slots, kMaxSlots);
+    B200V_REQUIRE(chunk_elems >= 1024 && chunk_elems <= ((size_t)1 << 30), B200V_ERR_INVALID,
+                  "chunk_elems %zu not in [1024, 2^30]", chunk_elems);
+    g_slots = slots;
+    g_chunk_elems = chunk_elems;
+    return B200V_OK;
+}
 
 int b200v_vector_add_host(const float* hA, const float* hB, float* hC, size_t n)
 {
@@ -426,9 +443,9 @@ int b200v_vector_add_host(const float* hA, const float* hB, float* hC, size_t n)
     if (int rc = pipe_init(p)) return rc;
 
     size_t k = 0;
-    for (size_t off = 0; off < n; off += kChunkElems, ++k) {
-        const int slot = (int)(k % kSlots);
-        const size_t m = std::min(kChunkElems, n - off);
+    for (size_t off = 0; off < n; off += p.chunk_elems, ++k) {
+        const int slot = (int)(k % p.slots);
+        const size_t m = std::min(p.chunk_elems, n - off);
         cudaStream_t st = p.stream[slot];
         // stream order makes the slot's previous D2H finish before its buffers are overwritten
         B200V_CUDA(cudaMemcpyAsync(p.a[slot], hA + off, m * sizeof(float), cudaMemcpyHostToDevice, st));
@@ -436,7 +453,7 @@ int b200v_vector_add_host(const float* hA, const float* hB, float* hC, size_t n)
         if (int rc = b200v_add_f32(p.c[slot], p.a[slot], p.b[slot], m, st)) return rc;
         B200V_CUDA(cudaMemcpyAsync(hC + off, p.c[slot], m * sizeof(float), cudaMemcpyDeviceToHost, st));
     }
-    for (int i = 0; i < kSlots; ++i) B200V_CUDA(cudaStreamSynchronize(p.stream[i]));
+    for (int i = 0; i < p.slots; ++i) B200V_CUDA(cudaStreamSynchronize(p.stream[i]));
     return B200V_OK;
 }
 

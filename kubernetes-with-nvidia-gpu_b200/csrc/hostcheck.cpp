@@ -42,7 +42,16 @@ inline float float_of(uint32_t u)
     return f;
 }
 
-template <int OP> inline float op1(float x, float y, float s)
+// The loops are compiled twice: a baseline x86-64 clone and an AVX2+FMA clone picked at load time.
+// With FMA in the ISA std::fmaf becomes one vfmadd instead of a libm call per element; both are
+// correctly rounded, so the clones agree bit for bit (tests/test_launcher_cpu.py cross-checks).
+#if defined(__x86_64__) && defined(__GNUC__)
+#define HOSTCHECK_CLONES __attribute__((target_clones("default", "arch=haswell")))
+#else
+#define HOSTCHECK_CLONES
+#endif
+
+template <int OP> inline __attribute__((always_inline)) float op1(float x, float y, float s)
 {
     if (OP == ADD) return x + y;
     if (OP == COPY) return x;
@@ -50,13 +59,13 @@ template <int OP> inline float op1(float x, float y, float s)
     return std::fmaf(s, x, y);  // correctly rounded whether or not the CPU has FMA
 }
 
-template <int OP> void loop_f32(float* d, const float* x, const float* y, float s, size_t n, bool par)
+template <int OP> HOSTCHECK_CLONES void loop_f32(float* d, const float* x, const float* y, float s, size_t n, bool par)
 {
 #pragma omp parallel for schedule(static) if (par)
     for (size_t i = 0; i < n; ++i) d[i] = op1<OP>(x[i], OP == ADD || OP == TRIAD ? y[i] : 0.0f, s);
 }
 
-template <int OP> void loop_bf16(uint16_t* d, const uint16_t* x, const uint16_t* y, float s, size_t n, bool par)
+template <int OP> HOSTCHECK_CLONES void loop_bf16(uint16_t* d, const uint16_t* x, const uint16_t* y, float s, size_t n, bool par)
 {
 #pragma omp parallel for schedule(static) if (par)
     for (size_t i = 0; i < n; ++i) {

@@ -2,7 +2,7 @@
 // CSV table (one row per configuration).  The product's csrc/tuning.h is set from these tables
 // (kept under profiles/).  Not part of the product; builds against the same stream_kernels.cuh.
 //
-//   tools/tune [log2_n=28] [iters=10] [stage=all|shape|hint|tma|ref]
+//   tools/tune [log2_n=28] [iters=10] [stage=all|shape|hint|tma|scale|small|ref]
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
@@ -173,6 +173,15 @@ int main(int argc, char** argv)
         add_shapes<OP_COPY, LD_NC_NA, ST_DEFAULT>("shape");
         add_shapes<OP_COPY, LD_DEFAULT, ST_DEFAULT>("shape");
     }
+    if (!strcmp(stage, "scale")) {
+        add_shapes<OP_SCALE, LD_NC_NA, ST_DEFAULT>("scale");
+        add_shapes<OP_SCALE, LD_DEFAULT, ST_DEFAULT>("scale");
+        add_shapes<OP_COPY, LD_DEFAULT, ST_DEFAULT>("scale");
+    }
+    if (!strcmp(stage, "small")) {   // sizes where the grid is only a few waves: which tile shape fills the SMs best
+        add_shapes<OP_ADD, LD_DEFAULT, ST_DEFAULT>("small");
+        add_shapes<OP_COPY, LD_DEFAULT, ST_DEFAULT>("small");
+    }
     if (all || !strcmp(stage, "hint")) {
         add_hints<OP_ADD, 32, 4, 256>("hint");
         add_hints<OP_ADD, 32, 2, 512>("hint");
@@ -219,7 +228,7 @@ int main(int argc, char** argv)
 
     const int ctas_modes[] = {0, 1, 2, 4, 8};
     for (const Config& cf : g_cfg) {
-        const double bytes = (cf.op == OP_COPY ? 8.0 : 12.0) * n;
+        const double bytes = (cf.op == OP_COPY || cf.op == OP_SCALE ? 8.0 : 12.0) * n;
         if (cf.smem > 0) {   // correctness of the TMA variant against the register kernel, once per config
             if (!cref) CK(cudaMalloc(&cref, n * 4));
             CK(cudaMemset(c, 0, n * 4));
@@ -238,6 +247,7 @@ int main(int argc, char** argv)
         }
         for (int cps : ctas_modes) {
             size_t tiles = n / cf.tile_elems;
+            if (tiles == 0) continue;
             size_t grid = tiles;
             if (cps > 0) grid = std::min(tiles, (size_t)sms * cps);
             if (cps * cf.block > 2048) continue;
