@@ -79,10 +79,23 @@ static int launch_stream(void* dst, const void* x, const void* y, float s, size_
     int sms = 0;
     if (int rc = current_sm_count(&sms)) return rc;
 
-    constexpr int BLOCK = TWO ? Tuning::kBlock2 : Tuning::kBlock1;
-    constexpr int UNROLL = TWO ? Tuning::kUnroll2 : Tuning::kUnroll1;
-    if (bits % 32 == 0) return launch_vec<OP, BF16, 32, UNROLL, BLOCK>(dst, x, y, s, n, sms, st);
-    if (bits % 16 == 0) return launch_vec<OP, BF16, 16, UNROLL * 2, BLOCK>(dst, x, y, s, n, sms, st);
+    const size_t bytes = n * ESZ;
+    if (bits % 32 == 0) {
+        if (bytes < Tuning::kMediumBytes)
+            return launch_vec<OP, BF16, 32, ShapeSmall::unroll, ShapeSmall::block>(dst, x, y, s, n, sms, st);
+        if (bytes < Tuning::kLargeBytes || OP == OP_COPY)
+            return launch_vec<OP, BF16, 32, ShapeMedium::unroll, ShapeMedium::block>(dst, x, y, s, n, sms, st);
+        if constexpr (TWO)
+            return launch_vec<OP, BF16, 32, ShapeLarge2::unroll, ShapeLarge2::block>(dst, x, y, s, n, sms, st);
+        else
+            return launch_vec<OP, BF16, 32, ShapeLargeScale::unroll, ShapeLargeScale::block>(dst, x, y, s, n, sms, st);
+    }
+    if (bits % 16 == 0) {
+        if constexpr (TWO)
+            return launch_vec<OP, BF16, 16, ShapeVec16Two::unroll, ShapeVec16Two::block>(dst, x, y, s, n, sms, st);
+        else
+            return launch_vec<OP, BF16, 16, ShapeVec16One::unroll, ShapeVec16One::block>(dst, x, y, s, n, sms, st);
+    }
     size_t grid = (n + 255) / 256;
     size_t cap = (size_t)sms * 32;
     if (grid > cap) grid = cap;

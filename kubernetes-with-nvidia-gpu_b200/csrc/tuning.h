@@ -13,22 +13,36 @@ namespace b200v {
 //              ld.global.nc variants: ptxas sinks the loads between the stores (40 regs instead
 //              of 80) and lands ~1-2 % lower (6982)
 //   copy       VECB=32 UNROLL=1 BLOCK=256, one tile per CTA                : 7033 GB/s
+//   scale      VECB=32 UNROLL=1 BLOCK=1024                                 : 7028 GB/s (BLOCK=256: 6877)
 //   for scale: cudaMemcpy D2D 6450 GB/s, cudaMemset 7061 GB/s on the same box
 // One tile per CTA wins everywhere: the block scheduler hands out tiles in address order, so the
 // set of tiles in flight is one contiguous window of each array.
+//
+// profiles/r01_tune_small_sizes.csv (2^20 .. 2^27 elements): the 64 KiB-per-array tile leaves too
+// few CTAs below 2^27 elements (one CTA per SM at 80 registers), so smaller tiles take over:
+//   add, 2^25 elements: <1,256> 6716  <2,256> 6553  <4,512> 6429
+//   add, 2^24 elements: <2,256> 6548  <1,256> 6438  <4,512> 5855
+//   add, 2^22 elements: <2,256> 8177 (L2-resident)  <4,512> 6858
+//   copy, 2^24 elements: <2,256> 6551  <1,256> 5954
 struct Tuning {
-    // two-input kernels (add, triad): 2 x UNROLL x 32 B in flight per thread
-    static constexpr int kBlock2 = 512;
-    static constexpr int kUnroll2 = 4;
-    // one-input kernels (copy, scale)
-    static constexpr int kBlock1 = 256;
-    static constexpr int kUnroll1 = 1;
     // plain (coherent) loads: program order is kept, every load of a tile is issued before the
     // first store
     static constexpr int kLd = LD_DEFAULT;
     static constexpr int kSt = ST_DEFAULT;
     // 0 = one tile per CTA (grid == tiles); k > 0 = persistent grid of k CTAs per SM
     static constexpr int kCtasPerSm = 0;
+    // bytes per array at which the launch shape changes
+    static constexpr size_t kLargeBytes = (size_t)512 << 20;
+    static constexpr size_t kMediumBytes = (size_t)128 << 20;
 };
+
+// <UNROLL, BLOCK> of the 256-bit kernel by op class and size class
+struct ShapeLarge2 { static constexpr int unroll = 4, block = 512; };    // add/triad, >= 512 MiB per array
+struct ShapeMedium { static constexpr int unroll = 1, block = 256; };    // every op, 128..512 MiB; copy above
+struct ShapeSmall { static constexpr int unroll = 2, block = 256; };     // every op, < 128 MiB
+struct ShapeLargeScale { static constexpr int unroll = 1, block = 1024; };  // scale, >= 512 MiB
+// 128-bit fallback for pointers that are 16- but not 32-byte aligned
+struct ShapeVec16Two { static constexpr int unroll = 4, block = 1024; };
+struct ShapeVec16One { static constexpr int unroll = 2, block = 256; };
 
 }  // namespace b200v
