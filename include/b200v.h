@@ -100,6 +100,8 @@ B200V_API int b200v_host_alloc(void **hptr, size_t bytes);      /* pinned */
 B200V_API int b200v_host_free(void *hptr);
 B200V_API int b200v_memcpy_h2d(void *dptr, const void *hptr, size_t bytes, void *stream);
 B200V_API int b200v_memcpy_d2h(void *hptr, const void *dptr, size_t bytes, void *stream);
+/* the driver's own device-to-device copy: the same-box comparator the sweep prints beside the kernels */
+B200V_API int b200v_memcpy_d2d(void *dst, const void *src, size_t bytes, void *stream);
 B200V_API int b200v_memset(void *dptr, int byte, size_t bytes, void *stream);
 B200V_API int b200v_stream_create(void **stream);
 B200V_API int b200v_stream_destroy(void *stream);

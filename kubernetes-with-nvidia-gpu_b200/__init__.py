@@ -88,6 +88,7 @@ def _signatures():
         "b200v_host_free": (i32, [vp]),
         "b200v_memcpy_h2d": (i32, [vp, vp, sz, vp]),
         "b200v_memcpy_d2h": (i32, [vp, vp, sz, vp]),
+        "b200v_memcpy_d2d": (i32, [vp, vp, sz, vp]),
         "b200v_memset": (i32, [vp, i32, sz, vp]),
         "b200v_stream_create": (i32, [pvp]),
         "b200v_stream_destroy": (i32, [vp]),

@@ -229,6 +229,14 @@ int b200v_memcpy_d2h(void* hptr, const void* dptr, size_t bytes, void* stream)
     return B200V_OK;
 }
 
+int b200v_memcpy_d2d(void* dst, const void* src, size_t bytes, void* stream)
+{
+    if (bytes == 0) return B200V_OK;
+    B200V_REQUIRE(dst && src, B200V_ERR_INVALID, "NULL pointer");
+    B200V_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, as_stream(stream)));
+    return B200V_OK;
+}
+
 int b200v_memset(void* dptr, int byte, size_t bytes, void* stream)
 {
     if (bytes == 0) return B200V_OK;

@@ -321,13 +321,42 @@ int mode_bench(const Args& a)
         printf("[bench] largest array limited to 2^%d bytes by free HBM\n", max_log2);
 
     FILE* js = a.json_path.empty() ? nullptr : fopen(a.json_path.c_str(), "w");
-    if (js) fprintf(js, "{\"gpu\": \"%s\", \"rows\": [\n", info.name);
+    if (js) fprintf(js, "{\"gpu\": \"%s\", ", info.name);
     bool first_row = true, all_ok = true;
 
     DevArrays v;
     TRY(alloc_arrays(v, (size_t)1 << max_log2));
+
+    // same-box reference points: the driver's device-to-device copy and memset at 1 GiB (or the largest size run)
+    double copy_gbs = a.measured_copy_gbs, memset_gbs = 0;
+    {
+        const size_t rb = (size_t)1 << std::min(max_log2, 30);
+        void *e0 = nullptr, *e1 = nullptr;
+        TRY(b200v_event_create(&e0));
+        TRY(b200v_event_create(&e1));
+        double best[2] = {1e30, 1e30};
+        for (int which = 0; which < 2; ++which)
+            for (int it = 0; it < a.warmup + 10; ++it) {
+                TRY(b200v_event_record(e0, nullptr));
+                if (which == 0) TRY(b200v_memcpy_d2d(v.d, v.x, rb, nullptr));
+                else TRY(b200v_memset(v.d, 1, rb, nullptr));
+                TRY(b200v_event_record(e1, nullptr));
+                TRY(b200v_event_sync(e1));
+                float ms = 0;
+                TRY(b200v_event_elapsed_ms(e0, e1, &ms));
+                if (it >= a.warmup) best[which] = std::min(best[which], (double)ms);
+            }
+        TRY(b200v_event_destroy(e0));
+        TRY(b200v_event_destroy(e1));
+        const double d2d = 2.0 * rb / best[0] * 1e-6;
+        memset_gbs = (double)rb / best[1] * 1e-6;
+        printf("[bench] same-box reference points at %zu MiB: cudaMemcpy D2D %.1f GB/s (read+write), cudaMemset %.1f GB/s\n",
+               rb >> 20, d2d, memset_gbs);
+        if (copy_gbs <= 0) copy_gbs = d2d;   // %copy column: against this run's own D2D copy unless a figure was passed in
+        if (js) fprintf(js, "\"memcpy_d2d_gbs\": %.1f, \"memset_gbs\": %.1f, \"copy_denominator_gbs\": %.1f, \"rows_follow\": true, \"rows\": [\n", d2d, memset_gbs, copy_gbs);
+    }
     printf("%-6s %-5s %12s %10s %10s %8s %10s", "op", "dtype", "bytes/array", "best ms", "GB/s", "%8TB/s", "b2b GB/s");
-    if (a.measured_copy_gbs > 0) printf(" %8s", "%copy");
+    printf(" %8s", "%copy");
     printf("  verify  note\n");
 
     const int ops[] = {B200V_OP_COPY, B200V_OP_SCALE, B200V_OP_ADD, B200V_OP_TRIAD};
@@ -370,7 +399,7 @@ int mode_bench(const Args& a)
                 // one event pair, which hides the per-launch latency that dominates the small rows
                 printf("%-6s %-5s %12zu %10.4f %10.1f %7.1f%% %10.1f", op_name(op), dtype == B200V_F32 ? "f32" : "bf16", bytes,
                        t.best_ms, gbs, 100.0 * gbs / kNominalGBs, (double)t.bytes_per_launch / t.mean_ms * 1e-6);
-                if (a.measured_copy_gbs > 0) printf(" %7.1f%%", 100.0 * gbs / a.measured_copy_gbs);
+                printf(" %7.1f%%", 100.0 * gbs / copy_gbs);
                 printf("  %-7s %s%s\n", ok ? how : "FAILED", resident ? "cache-resident (not an HBM number)" : "",
                        !resident && footprint <= 2 * info.l2_bytes ? "partly L2-resident" : "");
                 if (js) {

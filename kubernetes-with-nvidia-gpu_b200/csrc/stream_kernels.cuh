@@ -143,10 +143,20 @@ template <int OP> inline constexpr bool kReadsY = (OP == OP_ADD || OP == OP_TRIA
 //
 // n counts ELEMENTS.  dst/x/y must be VECB-aligned (the host dispatcher guarantees it).
 
-template <int OP, bool BF16, int VECB, int UNROLL, int BLOCK, int LDH, int STH>
+//
+// PDL = true adds the programmatic-dependent-launch handshake (griddepcontrol): the kernel lets
+// its stream successor become resident as soon as this grid's last CTAs are placed, and itself
+// touches no memory until its predecessor has completed and flushed.  Results are unchanged; what
+// it removes is the drain/launch bubble between back-to-back launches.
+
+template <int OP, bool BF16, int VECB, int UNROLL, int BLOCK, int LDH, int STH, bool PDL = false>
 __global__ void __launch_bounds__(BLOCK)
 stream_kernel(void* __restrict__ dst, const void* __restrict__ x, const void* __restrict__ y, float s, size_t n)
 {
+    if constexpr (PDL) {
+        asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+        asm volatile("griddepcontrol.wait;" ::: "memory");
+    }
     using V = Vec<VECB>;
     constexpr int WORDS = VECB / 4;
     constexpr size_t EPW = BF16 ? 2 : 1;                         // elements per 32-bit word

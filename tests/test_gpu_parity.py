@@ -156,6 +156,35 @@ def test_golden_vectors_through_the_gpu(L):
     # add with +0: widen(hi) + widen(lo-part) is not expressible either -> covered by add/triad above.
 
 
+def test_infinities_and_bf16_nan(L):
+    """Edge values the generator never emits.  fp32: +-Inf operands wherever the result is not a NaN
+    (NaN *payloads* are the one thing IEEE leaves open, and x86 and the GPU pick different ones, which
+    is why the workload keeps NaN-producing inputs out).  bf16: NaN results too, because both sides
+    canonicalise every NaN to 0x7FFF when rounding to bf16."""
+    inf, ninf, big, one, zero, nzero, den = 0x7F800000, 0xFF800000, 0x7F7FFFFF, 0x3F800000, 0, 0x80000000, 0x00000001
+    xs = np.array([inf, ninf, inf, big, big, one, den, zero, nzero, nzero, inf, ninf], dtype=np.uint32)
+    ys = np.array([one, big, inf, big, one, ninf, den, nzero, nzero, zero, big, ninf], dtype=np.uint32)
+    for op, s in (("add", 0.0), ("triad", 3.0), ("triad", -2.0), ("scale", 3.0), ("scale", -0.0), ("copy", 0.0)):
+        if op == "triad" and s < 0:
+            m = np.array([not (x in (inf, ninf) and y in (inf, ninf)) for x, y in zip(xs, ys)])  # drop inf-inf
+        elif op == "scale" and s == 0:
+            m = np.array([x not in (inf, ninf) for x in xs])                                      # drop 0*inf
+        else:
+            m = np.ones(len(xs), dtype=bool)
+        x, y = np.ascontiguousarray(xs[m]), np.ascontiguousarray(ys[m])
+        want = O.op(op, "f32", len(x), s=s, x=x, y=y)
+        assert not (((want & 0x7FFFFFFF) > 0x7F800000).any()), "test vector produces a NaN; fix the mask"
+        got = run_op(L, op, "f32", x, y if op in ("add", "triad") else None, s)
+        np.testing.assert_array_equal(got, want, err_msg=f"{op} s={s}")
+    hx = np.array([0x7F80, 0xFF80, 0x7F80, 0x7FC0, 0x7F7F, 0x0001, 0x8000, 0xFFFF, 0x7F80, 0x3F80], dtype=np.uint16)
+    hy = np.array([0xFF80, 0x7F80, 0x7F80, 0x3F80, 0x7F7F, 0x8001, 0x8000, 0x0000, 0x0000, 0x7FC1], dtype=np.uint16)
+    for op, s in (("add", 0.0), ("triad", 3.0), ("triad", 0.0), ("scale", 0.0), ("scale", -1.5)):
+        want = O.op(op, "bf16", len(hx), s=s, x=hx, y=hy)
+        got = run_op(L, op, "bf16", hx, hy if op in ("add", "triad") else None, s)
+        np.testing.assert_array_equal(got, want, err_msg=f"bf16 {op} s={s}")
+    assert (O.op("add", "bf16", len(hx), x=hx, y=hy)[:2] == 0x7FFF).all()          # inf-inf -> canonical NaN
+
+
 def test_argument_errors_on_device(L):
     buf = pkg.DeviceBuffer(1 << 20)
     p = buf.ptr

@@ -2,7 +2,7 @@
 // CSV table (one row per configuration).  The product's csrc/tuning.h is set from these tables
 // (kept under profiles/).  Not part of the product; builds against the same stream_kernels.cuh.
 //
-//   tools/tune [log2_n=28] [iters=10] [stage=all|shape|hint|tma|scale|small|ref]
+//   tools/tune [log2_n=28] [iters=10] [stage=all|shape|hint|tma|scale|small|pdl|ref]
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
@@ -64,6 +64,31 @@ static void add_cfg(const char* stage)
     c.regs = fa.numRegs;
     c.launch = [k](unsigned grid, void* d, const void* x, const void* y, float s, size_t n) {
         k<<<grid, BLOCK>>>(d, x, y, s, n);
+    };
+    g_cfg.push_back(c);
+}
+
+// the same register kernel launched with programmatic stream serialization (PDL); ld column = 9
+template <int OP, int VECB, int UNROLL, int BLOCK> static void add_pdl(const char* stage)
+{
+    Config c;
+    c.stage = stage;
+    c.op = OP; c.vecb = VECB; c.unroll = UNROLL; c.block = BLOCK; c.ldh = 9; c.sth = 0;
+    c.tile_elems = (size_t)BLOCK * UNROLL * (VECB / 4);
+    auto k = stream_kernel<OP, false, VECB, UNROLL, BLOCK, LD_DEFAULT, ST_DEFAULT, true>;
+    cudaFuncAttributes fa;
+    CK(cudaFuncGetAttributes(&fa, k));
+    c.regs = fa.numRegs;
+    c.launch = [k](unsigned grid, void* d, const void* x, const void* y, float s, size_t n) {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(grid);
+        cfg.blockDim = dim3(BLOCK);
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = at;
+        cfg.numAttrs = 1;
+        CK(cudaLaunchKernelEx(&cfg, k, d, x, y, s, n));
     };
     g_cfg.push_back(c);
 }
@@ -177,6 +202,18 @@ int main(int argc, char** argv)
         add_shapes<OP_SCALE, LD_NC_NA, ST_DEFAULT>("scale");
         add_shapes<OP_SCALE, LD_DEFAULT, ST_DEFAULT>("scale");
         add_shapes<OP_COPY, LD_DEFAULT, ST_DEFAULT>("scale");
+    }
+    if (!strcmp(stage, "pdl")) {
+        add_cfg<OP_ADD, 32, 4, 512, LD_DEFAULT, ST_DEFAULT>("pdl");
+        add_pdl<OP_ADD, 32, 4, 512>("pdl");
+        add_cfg<OP_ADD, 32, 1, 256, LD_DEFAULT, ST_DEFAULT>("pdl");
+        add_pdl<OP_ADD, 32, 1, 256>("pdl");
+        add_cfg<OP_ADD, 32, 2, 256, LD_DEFAULT, ST_DEFAULT>("pdl");
+        add_pdl<OP_ADD, 32, 2, 256>("pdl");
+        add_cfg<OP_COPY, 32, 1, 256, LD_DEFAULT, ST_DEFAULT>("pdl");
+        add_pdl<OP_COPY, 32, 1, 256>("pdl");
+        add_cfg<OP_COPY, 32, 2, 256, LD_DEFAULT, ST_DEFAULT>("pdl");
+        add_pdl<OP_COPY, 32, 2, 256>("pdl");
     }
     if (!strcmp(stage, "small")) {   // sizes where the grid is only a few waves: which tile shape fills the SMs best
         add_shapes<OP_ADD, LD_DEFAULT, ST_DEFAULT>("small");
