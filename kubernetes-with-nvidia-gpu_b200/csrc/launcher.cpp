@@ -885,6 +885,60 @@ int mode_p2p(const Args& a, bool print_verdict)
             fflush(stdout);
         }
     }
+    // All GPUs at once: in round k every GPU j pulls from GPU (j+k) mod g, so every NVLink port is
+    // busy in both directions and the switch carries g concurrent flows.  Kernels on different GPUs
+    // are independent (nobody waits on anybody); time = max over GPUs of the device-timed pull.
+    std::vector<double> ring_gbs;
+    {
+        std::vector<void*> e0((size_t)g), e1((size_t)g);
+        for (int j = 0; j < g; ++j) {
+            TRY(b200v_set_device(j));
+            TRY(b200v_event_create(&e0[j]));
+            TRY(b200v_event_create(&e1[j]));
+        }
+        printf("  concurrent rounds (every GPU pulls from its k-th neighbour at the same time):\n");
+        for (int k = 1; k < g; ++k) {
+            double worst = 0;
+            bool round_ok = true;
+            for (int rep = 0; rep < 3; ++rep) {
+                for (int j = 0; j < g; ++j) {
+                    TRY(b200v_set_device(j));
+                    TRY(b200v_event_record(e0[j], nullptr));
+                    TRY(b200v_peer_pull(dst[j], src[(j + k) % g], bytes, nullptr));
+                    TRY(b200v_event_record(e1[j], nullptr));
+                }
+                double slowest = 0;
+                for (int j = 0; j < g; ++j) {
+                    TRY(b200v_set_device(j));
+                    TRY(b200v_event_sync(e1[j]));
+                    float ms = 0;
+                    TRY(b200v_event_elapsed_ms(e0[j], e1[j], &ms));
+                    slowest = std::max(slowest, (double)ms);
+                }
+                if (rep == 0 || slowest < worst) worst = slowest;   // best of the repetitions, slowest GPU in each
+            }
+            for (int j = 0; j < g; ++j) {
+                TRY(b200v_set_device(j));
+                uint64_t got[2];
+                TRY(device_checksum(scratch[j], dst[j], bytes, 0, got));
+                const int i = (j + k) % g;
+                round_ok = round_ok && got[0] == want[2 * i] && got[1] == want[2 * i + 1];
+                TRY(b200v_memset(dst[j], 0xEE, bytes, nullptr));
+                TRY(b200v_device_sync());
+            }
+            const double per_gpu = bytes / worst * 1e-6;
+            ring_gbs.push_back(per_gpu);
+            ok = ok && round_ok;
+            printf("    shift %d: %.1f GB/s into every GPU at once (%.1f GB/s through the switch)  %s\n", k, per_gpu, per_gpu * g,
+                   round_ok ? "ok" : "FAILED");
+            fflush(stdout);
+        }
+        for (int j = 0; j < g; ++j) {
+            b200v_set_device(j);
+            b200v_event_destroy(e0[j]);
+            b200v_event_destroy(e1[j]);
+        }
+    }
     auto summary = [&](const char* name, std::vector<double> v) {
         std::sort(v.begin(), v.end());
         printf("[p2p] %-10s min %.1f  median %.1f  max %.1f GB/s per direction (%.1f%% of the %.0f GB/s NVLink 5 figure at the median)\n",
@@ -892,6 +946,7 @@ int mode_p2p(const Args& a, bool print_verdict)
     };
     summary("memcpyPeer", copy_gbs);
     summary("peer-load", pull_gbs);
+    if (!ring_gbs.empty()) summary("concurrent", ring_gbs);
     if (!a.json_path.empty()) {
         if (FILE* js = fopen((a.json_path + (a.mode == "full" ? ".p2p" : "")).c_str(), "w")) {
             fprintf(js, "{\"mode\": \"p2p\", \"gpus\": %d, \"bytes\": %zu, \"ok\": %s, \"pairs\": [", g, bytes, ok ? "true" : "false");
@@ -903,6 +958,8 @@ int mode_p2p(const Args& a, bool print_verdict)
                                 copy_gbs[k], pull_gbs[k]);
                         ++k;
                     }
+            fprintf(js, "], \"concurrent_shift_gbs_per_gpu\": [");
+            for (size_t q = 0; q < ring_gbs.size(); ++q) fprintf(js, "%s%.1f", q ? ", " : "", ring_gbs[q]);
             fprintf(js, "]}\n");
             fclose(js);
         }

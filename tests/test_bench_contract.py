@@ -1,0 +1,52 @@
+"""bench.py's JSON contract.  CPU tier: the reference arm (the CPU loop) prints the agreed keys.
+GPU tier: our arm prints one line with value/e2e/roofline/cpu_baseline/clocks and passes its own
+in-run parity checks."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+
+from b200v_pkg import ROOT
+
+BASE_KEYS = {"metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling",
+             "vs_baseline", "dtype", "data", "config", "e2e", "gpu_launches"}
+
+
+def run_bench(*args, timeout=600):
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), *args], capture_output=True, text=True, timeout=timeout)
+    assert r.returncode == 0, r.stderr[-3000:]
+    lines = [ln for ln in r.stdout.strip().splitlines() if ln.startswith("{")]
+    assert len(lines) == 1, r.stdout
+    return json.loads(lines[0])
+
+
+def test_reference_arm_line():
+    d = run_bench("--impl", "reference", "--steps", "2", "--warmup", "1")
+    assert BASE_KEYS <= set(d) and d["impl"] == "reference"
+    assert d["unit"] == "GB/s" and d["higher_is_better"] is True and d["vs_baseline"] is None and d["dtype"] == "f32"
+    assert d["e2e"] == {"value": d["value"], "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    cb = d["cpu_baseline"]
+    assert cb["kind"] == "port" and cb["cores"] >= 1 and cb["value"] == d["value"] and "2^" in cb["sample"]
+    assert "workload" in d["config"] and "model" not in d["config"]
+    assert d["value"] > 0.5 and d["gpu_launches"] == 0
+
+
+@pytest.mark.gpu
+def test_our_arm_line():
+    d = run_bench("--steps", "30", "--warmup", "3", "--e2e-steps", "2")
+    assert BASE_KEYS <= set(d) and "impl" not in d
+    assert d["metric"].startswith("vectorAdd/triad HBM GB/s") and d["scaling"] == "weak" and d["data"] == "synthetic"
+    assert d["n_gpus"] == 1 and d["steps"] == 30 and d["gpu_launches"] == 30
+    assert 3000 < d["value"] < 12000
+    rf = d["roofline"]
+    assert rf["bound"] == "hbm" and rf["unit"] == "GB/s" and abs(rf["frac"] - rf["achieved"] / rf["peak"]) < 1e-3
+    assert rf["algorithmic_bytes_per_launch"] == 12 << 28
+    e = d["e2e"]
+    assert e["h2d_bytes_per_step"] == 8 << 28 and e["d2h_bytes_per_step"] == 4 << 28 and 5 < e["value"] < 200
+    assert e["value"] < d["value"] / 10          # a host-buffer number, not a copy of the device-resident one
+    assert d["parity"]["device_window_bit_exact"] and d["parity"]["e2e_window_bit_exact"]
+    assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] >= 1
+    assert "sm_mhz" in d["clocks"] and "reasons" in d["clocks"]
+    assert "workload" in d["config"] and "model" not in d["config"]
