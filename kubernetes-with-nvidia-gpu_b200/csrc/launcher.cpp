@@ -39,6 +39,7 @@
 
 #include "b200v.h"
 #include "hostcheck.h"
+#include "nvml_probe.h"
 
 namespace {
 
@@ -62,6 +63,7 @@ struct Args {
     int gpus = 0;                // 0 = all visible
     uint32_t seed = 20261106u;
     bool inject_fault = false;
+    bool fail_on_throttle = false;   // burn-in: thermal / hardware slowdown reasons fail the run
     uint64_t p2p_bytes = 1ull << 30;
     int min_log2_bytes = 20, max_log2_bytes = 34;
     double measured_copy_gbs = 0.0;   // optional second denominator (--measured-copy-gbs)
@@ -160,6 +162,12 @@ int print_devices(int* count_out, bool all_details)
         if (all_details)
             printf("         SM clock %d MHz, memory clock %d MHz, bus %d bit, ECC %s\n", info.clock_khz / 1000,
                    info.mem_clock_khz / 1000, info.mem_bus_bits, info.ecc_enabled ? "on" : "off");
+        nvmlprobe::Sample nv;
+        if (nvmlprobe::sample(info.pci_bus_id, &nv))
+            printf("         now: SM %u MHz (max %u), memory %u MHz, %u C, %.0f W of %.0f W, clock limits: %s\n", nv.sm_mhz,
+                   nv.sm_max_mhz, nv.mem_mhz, nv.temp_c, nv.power_w, nv.power_limit_w, nvmlprobe::reasons_text(nv.reasons).c_str());
+        else if (d == 0 && all_details)
+            printf("         (NVML not loadable in this container: no live clocks / temperature / power)\n");
     }
     if (all_details && count > 1) {
         std::vector<int> m((size_t)count * count);
@@ -460,6 +468,10 @@ struct ShardResult {
     long passes = 0;
     int exit_code = EX_CUDA;
     std::string text;
+    // NVML readings over the run (burn-in): -1 = not available
+    int sm_min_mhz = -1, temp_max_c = -1;
+    double power_max_w = -1;
+    unsigned long long reasons = 0;
 };
 
 void child_say(const Args& a, const char* fmt, ...)
@@ -537,6 +549,9 @@ int mode_shard_child(const Args& a)
     int ok = 1;
     double best_ms = 0, mean_ms = 0;
     long passes = 0;
+    int nv_min_mhz = -1, nv_max_temp = -1;
+    double nv_max_power = -1;
+    unsigned long long nv_reasons = 0;
     if (!burnin) {
         b200v_timing t;
         memset(&t, 0, sizeof t);
@@ -555,7 +570,24 @@ int mode_shard_child(const Args& a)
         const double t_end = now_s() + a.seconds;
         double sum_ms = 0;
         best_ms = 1e30;
+        b200v_device_info dinfo;
+        memset(&dinfo, 0, sizeof dinfo);
+        dinfo.struct_size = sizeof dinfo;
+        const bool have_nvml = b200v_device_info_get(a.device, &dinfo) == B200V_OK && nvmlprobe::available();
+        double next_probe = 0;
         while (now_s() < t_end) {
+            if (have_nvml && now_s() >= next_probe) {   // a few readings per second while the GPU is loaded
+                nvmlprobe::Sample nv;
+                if (nvmlprobe::sample(dinfo.pci_bus_id, &nv)) {
+                    if (passes > 0) {                   // skip the idle reading before the first pass
+                        nv_min_mhz = nv_min_mhz < 0 ? (int)nv.sm_mhz : std::min(nv_min_mhz, (int)nv.sm_mhz);
+                        nv_reasons |= nv.reasons;
+                    }
+                    nv_max_temp = std::max(nv_max_temp, (int)nv.temp_c);
+                    nv_max_power = std::max(nv_max_power, nv.power_w);
+                }
+                next_probe = now_s() + 0.2;
+            }
             const int k = (int)(passes % 4);
             CTRY(b200v_event_record(e0, nullptr));
             CTRY(b200v_stream_op(op, dtype, v.d, v.x, two ? v.y : nullptr, kScalars[k], count, nullptr));
@@ -579,6 +611,7 @@ int mode_shard_child(const Args& a)
     }
     if (a.inject_fault && a.rank == a.world - 1) ok = 0;
     v.release();
+    if (nv_max_temp >= 0) child_say(a, "NVML %d %d %d %.1f %llu", a.rank, nv_min_mhz, nv_max_temp, nv_max_power, nv_reasons);
     child_say(a, "RESULT %d %d %.6f %.6f %" PRIu64 " %ld", a.rank, ok, best_ms, mean_ms, count, passes);
     return ok ? EX_PASS : EX_MISMATCH;
 }
@@ -702,6 +735,10 @@ int run_children(const Args& a, const char* child_mode, int world, std::vector<S
                 k->pending.erase(0, nl + 1);
                 if (line.rfind("READY", 0) == 0) {
                     k->ready = true;
+                } else if (line.rfind("NVML", 0) == 0) {
+                    ShardResult& q = k->res;
+                    int rk = 0;
+                    sscanf(line.c_str(), "NVML %d %d %d %lf %llu", &rk, &q.sm_min_mhz, &q.temp_max_c, &q.power_max_w, &q.reasons);
                 } else if (line.rfind("RESULT", 0) == 0) {
                     ShardResult& s = k->res;
                     sscanf(line.c_str(), "RESULT %d %d %lf %lf %" SCNu64 " %ld", &s.rank, &s.ok, &s.best_ms, &s.mean_ms, &s.count,
@@ -764,7 +801,7 @@ int mode_node(const Args& a, bool burnin, bool print_verdict)
     int rc = run_children(b, burnin ? "burnin-child" : "shard-child", world, res, 600.0 + 4 * a.seconds);
     if (rc != EX_PASS) return rc;
 
-    bool ok = true;
+    bool ok = true, throttled = false;
     double max_best = 0, max_mean = 0;
     uint64_t elems = 0;
     int worst_exit = EX_PASS;
@@ -776,6 +813,13 @@ int mode_node(const Args& a, bool burnin, bool print_verdict)
         printf("  rank %d (GPU %d): %" PRIu64 " elements, best %.4f ms (%.1f GB/s), mean %.4f ms, %ld passes, %s\n", s.rank, s.rank,
                s.count, s.best_ms, s.best_ms > 0 ? bytes / s.best_ms * 1e-6 : 0.0, s.mean_ms, s.passes,
                good ? "verified" : "FAILED");
+        if (s.temp_max_c >= 0) {
+            const bool bad = (s.reasons & nvmlprobe::kBadReasons) != 0;
+            printf("          under load: SM clock down to %d MHz, up to %d C, up to %.0f W, clock limits seen: %s%s\n", s.sm_min_mhz,
+                   s.temp_max_c, s.power_max_w, nvmlprobe::reasons_text(s.reasons).c_str(),
+                   bad ? "  <-- WARNING: thermal or hardware slowdown" : "");
+            throttled = throttled || bad;
+        }
         if (!s.text.empty()) printf("%s", s.text.c_str());
         max_best = std::max(max_best, s.best_ms);
         max_mean = std::max(max_mean, s.mean_ms);
@@ -797,13 +841,18 @@ int mode_node(const Args& a, bool burnin, bool print_verdict)
                     burnin ? "burnin" : "node", op_name(op), a.dtype.c_str(), world, elems, max_best, max_mean, node_gbs,
                     ok ? "true" : "false");
             for (size_t i = 0; i < res.size(); ++i)
-                fprintf(js, "%s{\"rank\": %d, \"ok\": %d, \"best_ms\": %.6f, \"mean_ms\": %.6f, \"elements\": %" PRIu64 ", \"passes\": %ld}",
-                        i ? ", " : "", res[i].rank, res[i].ok, res[i].best_ms, res[i].mean_ms, res[i].count, res[i].passes);
+                fprintf(js, "%s{\"rank\": %d, \"ok\": %d, \"best_ms\": %.6f, \"mean_ms\": %.6f, \"elements\": %" PRIu64 ", \"passes\": %ld, "
+                            "\"sm_min_mhz\": %d, \"temp_max_c\": %d, \"power_max_w\": %.1f, \"clock_limit_reasons\": \"%s\"}",
+                        i ? ", " : "", res[i].rank, res[i].ok, res[i].best_ms, res[i].mean_ms, res[i].count, res[i].passes,
+                        res[i].sm_min_mhz, res[i].temp_max_c, res[i].power_max_w,
+                        res[i].temp_max_c >= 0 ? nvmlprobe::reasons_text(res[i].reasons).c_str() : "unavailable");
             fprintf(js, "]}\n");
             fclose(js);
         }
     }
     if (!ok) return fail(worst_exit == EX_PASS ? EX_MISMATCH : worst_exit, "at least one rank failed");
+    if (throttled && a.fail_on_throttle)
+        return fail(EX_MISMATCH, "a GPU reported thermal or hardware slowdown under load (--fail-on-throttle)");
     return print_verdict ? pass() : EX_PASS;
 }
 
@@ -982,7 +1031,7 @@ void usage()
             "usage: gpu-validate [--mode smoke|list|bench|node|p2p|burnin|full|host-reference]\n"
             "                    [--device D] [--gpus G] [--n N | --log2n K] [--dtype f32|bf16] [--op add|copy|scale|triad]\n"
             "                    [--iters I] [--warmup W] [--seconds S] [--seed X] [--p2p-bytes B]\n"
-            "                    [--min-log2-bytes a --max-log2-bytes b] [--measured-copy-gbs G] [--json FILE] [--inject-fault]\n"
+            "                    [--min-log2-bytes a --max-log2-bytes b] [--measured-copy-gbs G] [--json FILE] [--inject-fault] [--fail-on-throttle]\n"
             "no arguments: vectorAdd N=50000 on GPU 0, prints Test PASSED / Test FAILED, exit code 0 / non-zero\n");
 }
 
@@ -997,6 +1046,7 @@ bool parse(int argc, char** argv, Args& a)
         };
         const char* v = nullptr;
         if (k == "--inject-fault") a.inject_fault = true;
+        else if (k == "--fail-on-throttle") a.fail_on_throttle = true;
         else if (k == "--quiet") a.quiet = true;
         else if (k == "--help" || k == "-h") return false;
         else if (!val(&v)) return false;

@@ -62,6 +62,7 @@ def test_list_mode(exe):
     assert r.returncode == 0
     assert re.search(r"GPU 0: NVIDIA B200 .* 148 SMs", r.stdout)
     assert "GPU-" in r.stdout and "driver API" in r.stdout
+    assert re.search(r"now: SM \d+ MHz \(max \d+\), memory \d+ MHz, \d+ C, \d+ W of \d+ W, clock limits:", r.stdout)
 
 
 def test_bench_mode_small_sweep(exe, tmp_path):
@@ -96,6 +97,9 @@ def test_burnin_mode_verifies_every_pass(exe, tmp_path):
     assert r.returncode == 0 and last_line(r) == "Test PASSED", r.stdout + r.stderr
     d = json.load(open(js))
     assert d["ok"] and d["ranks"][0]["passes"] >= 20
+    r0 = d["ranks"][0]                      # NVML readings taken while the GPU was loaded
+    assert r0["temp_max_c"] > 0 and r0["sm_min_mhz"] > 500 and r0["power_max_w"] > 50, r0
+    assert "under load: SM clock down to" in r.stdout
 
 
 def test_too_many_gpus_requested(exe):

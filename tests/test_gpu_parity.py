@@ -36,17 +36,19 @@ def esz(dtype):
 
 def run_op(L, op, dtype, x, y, s=3.0, offset_elems=0):
     """Upload bit patterns, run one kernel through the ABI, return the output bit patterns.
-    offset_elems shifts every array inside its allocation (alignment cases)."""
+    offset_elems shifts the arrays inside their allocations (alignment cases): one int for all
+    three, or a (dst, x, y) tuple."""
     n = len(x)
     e = esz(dtype)
-    pad = offset_elems * e
-    dx = pkg.DeviceBuffer(n * e + pad + 64).upload(x, pad)
-    dy = pkg.DeviceBuffer(n * e + pad + 64)
+    od, ox, oy = (offset_elems,) * 3 if isinstance(offset_elems, int) else offset_elems
+    dx = pkg.DeviceBuffer(n * e + ox * e + 64).upload(x, ox * e)
+    dy = pkg.DeviceBuffer(n * e + oy * e + 64)
     if y is not None:
-        dy.upload(y, pad)
+        dy.upload(y, oy * e)
+    pad = od * e
     dd = pkg.DeviceBuffer(n * e + pad + 64)
     pkg.check(L.b200v_memset(C.c_void_p(dd.ptr), 0xA5, dd.nbytes, None))
-    pkg.stream_op(op, dtype, dd.at(pad), dx.at(pad), dy.at(pad) if y is not None else None, s, n)
+    pkg.stream_op(op, dtype, dd.at(pad), dx.at(ox * e), dy.at(oy * e) if y is not None else None, s, n)
     pkg.check(L.b200v_device_sync())
     out = dd.download(pkg.NP_BITS[dtype], n, pad)
     guard = dd.download(np.uint8, 64, pad + n * e)
@@ -117,6 +119,27 @@ def test_ops_on_unaligned_views(L, dtype, offset):
         want = O.op(op, dtype, n, s=3.0, x=x, y=y)
         got = run_op(L, op, dtype, x, y if op in ("add", "triad") else None, 3.0, offset_elems=offset)
         np.testing.assert_array_equal(got, want, err_msg=f"{op} {dtype} offset={offset}")
+
+
+def test_random_shapes_and_alignments(L):
+    """Seeded fuzz: random op, dtype, generator mode, scalar, length and an independent element
+    offset for each of the three arrays (so the 256-bit, 128-bit and element-wise dispatch paths are
+    all hit with mixed alignments)."""
+    rng = np.random.default_rng(20261106)
+    ops = ["add", "copy", "scale", "triad"]
+    scalars = [3.0, -0.75, 1.0009765625, 0.333251953125, -2.5e-20, 6.0e18]
+    for case in range(120):
+        op = ops[rng.integers(4)]
+        dtype = "f32" if rng.integers(2) else "bf16"
+        mode = int(rng.integers(3))
+        n = int(rng.integers(1, 400_000)) if case % 4 else int(rng.integers(1, 70))
+        offs = tuple(int(v) for v in rng.integers(0, 17, size=3))
+        s = scalars[rng.integers(len(scalars))]
+        x = O.fill(dtype, int(rng.integers(0, 1 << 40)), n, SEED + case, 0, mode)
+        y = O.fill(dtype, int(rng.integers(0, 1 << 40)), n, SEED + case, 1, mode)
+        want = O.op(op, dtype, n, s=s, x=x, y=y)
+        got = run_op(L, op, dtype, x, y if op in ("add", "triad") else None, s, offset_elems=offs)
+        np.testing.assert_array_equal(got, want, err_msg=f"case {case}: {op} {dtype} mode={mode} n={n} offs={offs} s={s}")
 
 
 def test_golden_vectors_through_the_gpu(L):
@@ -298,6 +321,35 @@ def test_baseline_size_checksum_and_windows(L, op, dtype, log2n):
         np.testing.assert_array_equal(dd.download(pkg.NP_BITS[dtype], m, woff * e), O.op(op, dtype, m, s=3.0, x=x, y=y))
     for b in (dx, dy, dd):
         b.free()
+
+
+def test_full_2p32_triad_one_gpu(L):
+    """BASELINE.json configs[3] at its full size on one GPU: triad over 2^32 fp32 elements (3 x 16 GiB),
+    whole-output checksum against the host oracle computed in chunks on all host cores, plus windows
+    on both sides of element 2^31 and at the very end (64-bit indexing)."""
+    n = 1 << 32
+    info = pkg.device_info(0)
+    if info.hbm_free_bytes < 50 << 30:
+        pytest.skip("needs 48 GiB of free HBM")
+    vp = C.c_void_p
+    dx, dy, dd = (pkg.DeviceBuffer(4 * n) for _ in range(3))
+    pkg.check(L.b200v_fill(pkg.F32, vp(dx.ptr), 0, n, SEED, 0, O.GEN_UNIT, None))
+    pkg.check(L.b200v_fill(pkg.F32, vp(dy.ptr), 0, n, SEED, 1, O.GEN_UNIT, None))
+    pkg.check(L.b200v_triad_f32(vp(dd.ptr), 3.0, vp(dx.ptr), vp(dy.ptr), n, None))
+    got = [0, 0]
+    piece = 1 << 30                      # device checksum in 4 GiB pieces (the no-workspace entry's limit), summed
+    ws = pkg.DeviceBuffer(L.b200v_checksum_workspace_bytes())
+    for off in range(0, n, piece):
+        c = pkg.checksum(dd.at(4 * off), 4 * piece, off, ws)
+        got = [(got[0] + c[0]) & M64, (got[1] + c[1]) & M64]
+    for woff in (0, (1 << 31) - 32_768, n - 65_536):
+        m = 65_536
+        x = O.fill("f32", woff, m, SEED, 0)
+        y = O.fill("f32", woff, m, SEED, 1)
+        np.testing.assert_array_equal(dd.download(np.uint32, m, 4 * woff), O.op("triad", "f32", m, s=3.0, x=x, y=y))
+    for b in (dx, dy, dd, ws):
+        b.free()
+    assert tuple(got) == oracle_checksum_chunked("triad", "f32", n, 0, 3.0, chunk=1 << 26)
 
 
 def test_time_op_reports_device_times(L):
