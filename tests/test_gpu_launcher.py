@@ -32,9 +32,13 @@ def ngpus():
 
 def test_default_pod_run(exe):
     """No arguments = the Step 9 contract: GPU listed, vectorAdd N=50,000 verified, Test PASSED, exit 0."""
+    import time
+    t0 = time.perf_counter()
     r = run(exe)
+    elapsed = time.perf_counter() - t0
     assert r.returncode == 0, r.stdout + r.stderr
     assert last_line(r) == "Test PASSED"
+    assert elapsed < 15.0, f"default run took {elapsed:.1f} s; the guide reads the log after `sleep 15` (reference README.md:326)"
     assert "NVIDIA B200" in r.stdout and "sm_100" in r.stdout
     assert "50000 of 50000 elements bit-identical" in r.stdout
 

@@ -2,7 +2,7 @@
 // CSV table (one row per configuration).  The product's csrc/tuning.h is set from these tables
 // (kept under profiles/).  Not part of the product; builds against the same stream_kernels.cuh.
 //
-//   tools/tune [log2_n=28] [iters=10] [stage=all|shape|hint|tma|scale|small|pdl|ref]
+//   tools/tune [log2_n=28] [iters=10] [stage=all|shape|hint|tma|scale|small|pdl|bf16|ref]
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
@@ -51,21 +51,41 @@ struct Config {
 
 static std::vector<Config> g_cfg;
 
-template <int OP, int VECB, int UNROLL, int BLOCK, int LDH, int STH>
+// BF16 = true: the arrays are read as bf16 (2 elements per word); n passed to the kernel is doubled so
+// the bytes moved are the same as in the fp32 rows
+template <int OP, int VECB, int UNROLL, int BLOCK, int LDH, int STH, bool BF16 = false>
 static void add_cfg(const char* stage)
 {
     Config c;
     c.stage = stage;
     c.op = OP; c.vecb = VECB; c.unroll = UNROLL; c.block = BLOCK; c.ldh = LDH; c.sth = STH;
     c.tile_elems = (size_t)BLOCK * UNROLL * (VECB / 4);
-    auto k = stream_kernel<OP, false, VECB, UNROLL, BLOCK, LDH, STH>;
+    auto k = stream_kernel<OP, BF16, VECB, UNROLL, BLOCK, LDH, STH>;
     cudaFuncAttributes fa;
     CK(cudaFuncGetAttributes(&fa, k));
     c.regs = fa.numRegs;
     c.launch = [k](unsigned grid, void* d, const void* x, const void* y, float s, size_t n) {
-        k<<<grid, BLOCK>>>(d, x, y, s, n);
+        k<<<grid, BLOCK>>>(d, x, y, s, BF16 ? 2 * n : n);
     };
     g_cfg.push_back(c);
+}
+
+template <int OP> static void add_bf16_shapes(const char* stage)
+{
+    add_cfg<OP, 32, 1, 256, LD_DEFAULT, ST_DEFAULT, true>(stage);
+    add_cfg<OP, 32, 2, 256, LD_DEFAULT, ST_DEFAULT, true>(stage);
+    add_cfg<OP, 32, 4, 256, LD_DEFAULT, ST_DEFAULT, true>(stage);
+    add_cfg<OP, 32, 1, 512, LD_DEFAULT, ST_DEFAULT, true>(stage);
+    add_cfg<OP, 32, 2, 512, LD_DEFAULT, ST_DEFAULT, true>(stage);
+    add_cfg<OP, 32, 4, 512, LD_DEFAULT, ST_DEFAULT, true>(stage);
+    add_cfg<OP, 32, 1, 1024, LD_DEFAULT, ST_DEFAULT, true>(stage);
+    add_cfg<OP, 32, 2, 1024, LD_DEFAULT, ST_DEFAULT, true>(stage);
+    add_cfg<OP, 32, 2, 128, LD_DEFAULT, ST_DEFAULT, true>(stage);
+    add_cfg<OP, 32, 4, 128, LD_DEFAULT, ST_DEFAULT, true>(stage);
+    add_cfg<OP, 16, 4, 512, LD_DEFAULT, ST_DEFAULT, true>(stage);
+    add_cfg<OP, 16, 4, 1024, LD_DEFAULT, ST_DEFAULT, true>(stage);
+    add_cfg<OP, 32, 4, 512, LD_NC_NA, ST_DEFAULT, true>(stage);
+    add_cfg<OP, 32, 2, 512, LD_NC_NA, ST_DEFAULT, true>(stage);
 }
 
 // the same register kernel launched with programmatic stream serialization (PDL); ld column = 9
@@ -202,6 +222,14 @@ int main(int argc, char** argv)
         add_shapes<OP_SCALE, LD_NC_NA, ST_DEFAULT>("scale");
         add_shapes<OP_SCALE, LD_DEFAULT, ST_DEFAULT>("scale");
         add_shapes<OP_COPY, LD_DEFAULT, ST_DEFAULT>("scale");
+    }
+    if (!strcmp(stage, "bf16")) {   // rows are bf16 kernels over the same bytes; fp32 rows of the shipped shapes for comparison
+        add_bf16_shapes<OP_ADD>("bf16");
+        add_bf16_shapes<OP_TRIAD>("bf16");
+        add_bf16_shapes<OP_SCALE>("bf16");
+        add_cfg<OP_ADD, 32, 4, 512, LD_DEFAULT, ST_DEFAULT>("f32ref");
+        add_cfg<OP_TRIAD, 32, 4, 512, LD_DEFAULT, ST_DEFAULT>("f32ref");
+        add_cfg<OP_SCALE, 32, 1, 1024, LD_DEFAULT, ST_DEFAULT>("f32ref");
     }
     if (!strcmp(stage, "pdl")) {
         add_cfg<OP_ADD, 32, 4, 512, LD_DEFAULT, ST_DEFAULT>("pdl");
