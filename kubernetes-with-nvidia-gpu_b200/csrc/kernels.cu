@@ -97,10 +97,10 @@ static int launch_stream(void* dst, const void* x, const void* y, float s, size_
             return launch_vec<OP, BF16, 32, ShapeSmall::unroll, ShapeSmall::block>(dst, x, y, s, n, sms, st);
         if (bytes < Tuning::kLargeBytes || OP == OP_COPY)
             return launch_vec<OP, BF16, 32, ShapeMedium::unroll, ShapeMedium::block>(dst, x, y, s, n, sms, st);
-        if constexpr (TWO)
+        if constexpr (TWO && !BF16)
             return launch_vec<OP, BF16, 32, ShapeLarge2::unroll, ShapeLarge2::block>(dst, x, y, s, n, sms, st);
-        else
-            return launch_vec<OP, BF16, 32, ShapeLargeScale::unroll, ShapeLargeScale::block>(dst, x, y, s, n, sms, st);
+        else   // scale, and the bf16 two-input kernels (profiles/r01_tune_bf16.csv)
+            return launch_vec<OP, BF16, 32, ShapeLarge1024::unroll, ShapeLarge1024::block>(dst, x, y, s, n, sms, st);
     }
     if (bits % 16 == 0) {
         if constexpr (TWO)

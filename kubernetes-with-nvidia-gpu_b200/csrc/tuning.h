@@ -37,10 +37,12 @@ struct Tuning {
 };
 
 // <UNROLL, BLOCK> of the 256-bit kernel by op class and size class
-struct ShapeLarge2 { static constexpr int unroll = 4, block = 512; };    // add/triad, >= 512 MiB per array
+struct ShapeLarge2 { static constexpr int unroll = 4, block = 512; };    // fp32 add/triad, >= 512 MiB per array
 struct ShapeMedium { static constexpr int unroll = 1, block = 256; };    // every op, 128..512 MiB; copy above
 struct ShapeSmall { static constexpr int unroll = 2, block = 256; };     // every op, < 128 MiB
-struct ShapeLargeScale { static constexpr int unroll = 1, block = 1024; };  // scale, >= 512 MiB
+// scale, and bf16 add/triad (the unpack/convert code lets ptxas interleave the <4,512> loads anyway:
+// 60 registers, 6999 GB/s; <1,1024> reaches 7088 at the same bytes), >= 512 MiB
+struct ShapeLarge1024 { static constexpr int unroll = 1, block = 1024; };
 // 128-bit fallback for pointers that are 16- but not 32-byte aligned
 struct ShapeVec16Two { static constexpr int unroll = 4, block = 1024; };
 struct ShapeVec16One { static constexpr int unroll = 2, block = 256; };
