@@ -75,7 +75,7 @@ typedef struct b200v_device_info {
     int32_t  mem_clock_khz;
     int32_t  mem_bus_bits;
     uint64_t hbm_bytes;
-    uint64_t hbm_free_bytes;
+    uint64_t hbm_free_bytes;       /* filled for the CURRENT device only (needs a context); else 0 */
     uint64_t l2_bytes;
     int32_t  driver_version;       /* cudaDriverGetVersion, e.g. 13000                       */
     int32_t  runtime_version;      /* cudaRuntimeGetVersion, e.g. 12090                      */

@@ -130,13 +130,13 @@ int b200v_device_info_get(int device, b200v_device_info* info)
     info->ecc_enabled = p.ECCEnabled;
     B200V_CUDA(cudaDriverGetVersion(&info->driver_version));
     B200V_CUDA(cudaRuntimeGetVersion(&info->runtime_version));
-    int prev = 0;
-    B200V_CUDA(cudaGetDevice(&prev));
-    B200V_CUDA(cudaSetDevice(device));
+    // Free memory needs a context on the device.  Only the current device is asked, so that listing
+    // the GPUs of an 8-GPU node does not create eight contexts (the default pod run must stay well
+    // inside the 15 s of reference README.md:326); hbm_free_bytes stays 0 = "not queried" elsewhere.
+    int cur = -1;
+    B200V_CUDA(cudaGetDevice(&cur));
     size_t free_b = 0, total_b = 0;
-    cudaError_t e = cudaMemGetInfo(&free_b, &total_b);
-    (void)cudaSetDevice(prev);
-    if (e != cudaSuccess) return cuda_status(e, "cudaMemGetInfo", __FILE__, __LINE__);
+    if (cur == device) B200V_CUDA(cudaMemGetInfo(&free_b, &total_b));
     info->hbm_free_bytes = free_b;
     return B200V_OK;
 }

@@ -150,15 +150,20 @@ int print_devices(int* count_out, bool all_details)
     for (int d = 0; d < count; ++d) {
         memset(&info, 0, sizeof info);
         info.struct_size = sizeof info;
+        // the detailed listing visits every device (and so creates a context on each) to read its
+        // free memory; the short one leaves the other GPUs untouched
+        if (all_details && (st = b200v_set_device(d)) != B200V_OK) return st;
         st = b200v_device_info_get(d, &info);
         if (st != B200V_OK) return st;
         if (d == 0)
             printf("[discovery] %d CUDA device%s visible; driver API %d.%d, runtime %d.%d\n", count, count == 1 ? "" : "s",
                    info.driver_version / 1000, (info.driver_version % 1000) / 10, info.runtime_version / 1000,
                    (info.runtime_version % 1000) / 10);
-        printf("  GPU %d: %s  sm_%d%d  %d SMs  %.0f MiB HBM (%.0f MiB free)  L2 %.0f MiB  %s  %s\n", d, info.name,
-               info.cc_major, info.cc_minor, info.sm_count, info.hbm_bytes / 1048576.0, info.hbm_free_bytes / 1048576.0,
-               info.l2_bytes / 1048576.0, info.pci_bus_id, info.uuid);
+        char free_txt[48] = "";
+        if (info.hbm_free_bytes) snprintf(free_txt, sizeof free_txt, " (%.0f MiB free)", info.hbm_free_bytes / 1048576.0);
+        printf("  GPU %d: %s  sm_%d%d  %d SMs  %.0f MiB HBM%s  L2 %.0f MiB  %s  %s\n", d, info.name, info.cc_major,
+               info.cc_minor, info.sm_count, info.hbm_bytes / 1048576.0, free_txt, info.l2_bytes / 1048576.0, info.pci_bus_id,
+               info.uuid);
         if (all_details)
             printf("         SM clock %d MHz, memory clock %d MHz, bus %d bit, ECC %s\n", info.clock_khz / 1000,
                    info.mem_clock_khz / 1000, info.mem_bus_bits, info.ecc_enabled ? "on" : "off");
@@ -169,6 +174,7 @@ int print_devices(int* count_out, bool all_details)
         else if (d == 0 && all_details)
             printf("         (NVML not loadable in this container: no live clocks / temperature / power)\n");
     }
+    if (all_details) b200v_set_device(0);
     if (all_details && count > 1) {
         std::vector<int> m((size_t)count * count);
         if (b200v_peer_matrix(count, m.data()) == B200V_OK) {
@@ -318,7 +324,7 @@ int mode_bench(const Args& a)
     if (a.device >= count) return fail(EX_NO_DEVICE, "device %d requested, %d visible", a.device, count);
     TRY(b200v_set_device(a.device));
     TRY(b200v_require_sm100(a.device));
-    b200v_device_info info;
+    b200v_device_info info;   // queried again now that a.device is current: free memory is filled in
     memset(&info, 0, sizeof info);
     info.struct_size = sizeof info;
     TRY(b200v_device_info_get(a.device, &info));
