@@ -1,0 +1,407 @@
+// mode_node.cpp — `gpu-validate --mode node|burnin`: one process per GPU (BASELINE.json configs[3] and
+// the burn-in half of configs[4]).  The parent forks and execs one child per GPU before it touches CUDA,
+// releases them together once all are initialised, and reduces max(ms) / AND(verified) over pipes.
+#include "launcher_common.h"
+
+namespace gpuvalidate {
+
+// ----------------------------------------------------------------------------------------------
+// shard child: one process, one GPU, one contiguous shard of the global vector
+
+struct ShardResult {
+    int rank = -1;
+    int ok = 0;
+    double best_ms = 0, mean_ms = 0;
+    uint64_t count = 0;
+    long passes = 0;
+    int exit_code = EX_CUDA;
+    std::string text;
+    // NVML readings over the run (burn-in): -1 = not available
+    int sm_min_mhz = -1, temp_max_c = -1;
+    double power_max_w = -1;
+    unsigned long long reasons = 0;
+};
+
+void child_say(const Args& a, const char* fmt, ...)
+{
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    int len = vsnprintf(buf, sizeof buf - 1, fmt, ap);
+    va_end(ap);
+    if (len < 0) return;
+    len = std::min(len, (int)sizeof buf - 2);
+    buf[len++] = '\n';
+    if (a.out_fd >= 0) {
+        ssize_t r = write(a.out_fd, buf, (size_t)len);
+        (void)r;
+    } else {
+        fwrite(buf, 1, (size_t)len, stdout);
+        fflush(stdout);
+    }
+}
+
+int child_fail(const Args& a, int status, const char* what)
+{
+    child_say(a, "ERROR %d %d %s: %s: %s", a.rank, exit_code_for(status), what, b200v_status_name(status), b200v_last_error());
+    return exit_code_for(status);
+}
+
+#define CTRY(call)                                            \
+    do {                                                      \
+        int st__ = (call);                                    \
+        if (st__ != B200V_OK) return child_fail(a, st__, #call); \
+    } while (0)
+
+// scalars rotated between burn-in passes so a stale output can never pass verification
+const float kScalars[4] = {3.0f, -0.75f, 1.0009765625f, 2.5f};
+
+int mode_shard_child(const Args& a)
+{
+    const bool burnin = a.mode == "burnin-child";
+    const int dtype = dtype_id(a.dtype);
+    const int op = a.op.empty() ? B200V_OP_TRIAD : op_id(a.op);
+    CTRY(b200v_set_device(a.device));
+    CTRY(b200v_require_sm100(a.device));
+    const uint64_t total = a.log2n >= 0 ? (1ull << a.log2n) : a.n;
+    uint64_t begin = 0, count = 0;
+    CTRY(b200v_shard_range(total, a.rank, a.world, &begin, &count));
+    if (dtype == B200V_BF16 && (begin & 1)) {   // keep bf16 shards on 32-bit word boundaries
+        begin += 1;
+        count -= count ? 1 : 0;
+    }
+    const size_t bytes = (size_t)count * esize(dtype);
+    DevArrays v;
+    CTRY(alloc_arrays(v, bytes));
+    CTRY(b200v_fill(dtype, v.x, begin, count, a.seed, 0, B200V_GEN_UNIT, nullptr));
+    CTRY(b200v_fill(dtype, v.y, begin, count, a.seed, 1, B200V_GEN_UNIT, nullptr));
+    const bool two = op == B200V_OP_ADD || op == B200V_OP_TRIAD;
+    for (int i = 0; i < a.warmup; ++i) CTRY(b200v_stream_op(op, dtype, v.d, v.x, two ? v.y : nullptr, kScalars[0], count, nullptr));
+    CTRY(b200v_device_sync());
+
+    // expected checksums from the host loop (word indices are shard-local)
+    const int nscal = burnin ? 4 : 1;
+    uint64_t want[4][2];
+    for (int k = 0; k < nscal; ++k)
+        hostcheck::expected_checksum(op, dtype, begin, count, a.seed, hostcheck::UNIT, kScalars[k], 0, want[k]);
+
+    // start barrier: tell the parent we are ready, wait for its go byte
+    child_say(a, "READY %d", a.rank);
+    if (a.go_fd >= 0) {
+        char c;
+        ssize_t r;
+        do r = read(a.go_fd, &c, 1); while (r < 0 && errno == EINTR);
+        if (r != 1) return child_fail(a, B200V_ERR_INVALID, "start barrier closed");
+    }
+
+    int ok = 1;
+    double best_ms = 0, mean_ms = 0;
+    long passes = 0;
+    int nv_min_mhz = -1, nv_max_temp = -1;
+    double nv_max_power = -1;
+    unsigned long long nv_reasons = 0;
+    if (!burnin) {
+        b200v_timing t;
+        memset(&t, 0, sizeof t);
+        t.struct_size = sizeof t;
+        CTRY(b200v_time_op(op, dtype, v.d, v.x, two ? v.y : nullptr, kScalars[0], count, 0, a.iters, nullptr, &t));
+        best_ms = t.best_ms;
+        mean_ms = t.mean_ms;
+        passes = 2L * a.iters;
+        uint64_t got[2];
+        CTRY(device_checksum(v, v.d, bytes, 0, got));
+        ok = got[0] == want[0][0] && got[1] == want[0][1];
+    } else {
+        void *e0 = nullptr, *e1 = nullptr;
+        CTRY(b200v_event_create(&e0));
+        CTRY(b200v_event_create(&e1));
+        const double t_end = now_s() + a.seconds;
+        double sum_ms = 0;
+        best_ms = 1e30;
+        b200v_device_info dinfo;
+        memset(&dinfo, 0, sizeof dinfo);
+        dinfo.struct_size = sizeof dinfo;
+        const bool have_nvml = b200v_device_info_get(a.device, &dinfo) == B200V_OK && nvmlprobe::available();
+        double next_probe = 0;
+        while (now_s() < t_end) {
+            if (have_nvml && now_s() >= next_probe) {   // a few readings per second while the GPU is loaded
+                nvmlprobe::Sample nv;
+                if (nvmlprobe::sample(dinfo.pci_bus_id, &nv)) {
+                    if (passes > 0) {                   // skip the idle reading before the first pass
+                        nv_min_mhz = nv_min_mhz < 0 ? (int)nv.sm_mhz : std::min(nv_min_mhz, (int)nv.sm_mhz);
+                        nv_reasons |= nv.reasons;
+                    }
+                    nv_max_temp = std::max(nv_max_temp, (int)nv.temp_c);
+                    nv_max_power = std::max(nv_max_power, nv.power_w);
+                }
+                next_probe = now_s() + 0.2;
+            }
+            const int k = (int)(passes % 4);
+            CTRY(b200v_event_record(e0, nullptr));
+            CTRY(b200v_stream_op(op, dtype, v.d, v.x, two ? v.y : nullptr, kScalars[k], count, nullptr));
+            CTRY(b200v_event_record(e1, nullptr));
+            uint64_t got[2];
+            CTRY(device_checksum(v, v.d, bytes, 0, got));
+            float ms = 0;
+            CTRY(b200v_event_elapsed_ms(e0, e1, &ms));
+            best_ms = std::min(best_ms, (double)ms);
+            sum_ms += ms;
+            ++passes;
+            if (got[0] != want[k][0] || got[1] != want[k][1]) {
+                ok = 0;
+                child_say(a, "NOTE %d pass %ld failed verification", a.rank, passes);
+                break;
+            }
+        }
+        mean_ms = passes ? sum_ms / passes : 0;
+        b200v_event_destroy(e0);
+        b200v_event_destroy(e1);
+    }
+    if (a.inject_fault && a.rank == a.world - 1) ok = 0;
+    v.release();
+    if (nv_max_temp >= 0) child_say(a, "NVML %d %d %d %.1f %llu", a.rank, nv_min_mhz, nv_max_temp, nv_max_power, nv_reasons);
+    child_say(a, "RESULT %d %d %.6f %.6f %" PRIu64 " %ld", a.rank, ok, best_ms, mean_ms, count, passes);
+    return ok ? EX_PASS : EX_MISMATCH;
+}
+
+// ----------------------------------------------------------------------------------------------
+// node / burnin parent: fork+exec one child per GPU *before* touching CUDA in this process.
+
+int probe_device_count()
+{
+    // a throw-away child asks the runtime, so this process never holds a CUDA context across fork()
+    int fds[2];
+    if (pipe(fds) != 0) return -1;
+    pid_t pid = fork();
+    if (pid < 0) return -1;
+    if (pid == 0) {
+        close(fds[0]);
+        int n = 0;
+        if (b200v_device_count(&n) != B200V_OK) n = 0;
+        ssize_t r = write(fds[1], &n, sizeof n);
+        (void)r;
+        _exit(0);
+    }
+    close(fds[1]);
+    int n = 0;
+    ssize_t r = read(fds[0], &n, sizeof n);
+    close(fds[0]);
+    int wst = 0;
+    waitpid(pid, &wst, 0);
+    return r == (ssize_t)sizeof n ? n : -1;
+}
+
+struct Child {
+    pid_t pid = -1;
+    int go_w = -1, out_r = -1;
+    std::string pending;
+    bool ready = false, done = false;
+    ShardResult res;
+};
+
+int run_children(const Args& a, const char* child_mode, int world, std::vector<ShardResult>& results, double timeout_s)
+{
+    char self[4096];
+    ssize_t len = readlink("/proc/self/exe", self, sizeof self - 1);
+    if (len <= 0) return fail(EX_CUDA, "cannot resolve /proc/self/exe");
+    self[len] = 0;
+
+    std::vector<Child> kids((size_t)world);
+    const int threads = std::max(1, hostcheck::max_threads() / world);
+    for (int r = 0; r < world; ++r) {
+        int go[2], out[2];
+        if (pipe(go) != 0 || pipe(out) != 0) return fail(EX_CUDA, "pipe: %s", strerror(errno));
+        pid_t pid = fork();
+        if (pid < 0) return fail(EX_CUDA, "fork: %s", strerror(errno));
+        if (pid == 0) {
+            close(go[1]);
+            close(out[0]);
+            for (int q = 0; q < r; ++q) {
+                close(kids[q].go_w);
+                close(kids[q].out_r);
+            }
+            char b[16][64];
+            snprintf(b[0], 64, "%d", r);
+            snprintf(b[1], 64, "%d", world);
+            snprintf(b[2], 64, "%d", r);   // device = rank among the GPUs this container was granted
+            snprintf(b[3], 64, "%d", go[0]);
+            snprintf(b[4], 64, "%d", out[1]);
+            snprintf(b[5], 64, "%d", a.log2n);
+            snprintf(b[6], 64, "%" PRIu64, a.n);
+            snprintf(b[7], 64, "%d", a.iters);
+            snprintf(b[8], 64, "%d", a.warmup);
+            snprintf(b[9], 64, "%.3f", a.seconds);
+            snprintf(b[10], 64, "%u", a.seed);
+            snprintf(b[11], 64, "%d", threads);
+            setenv("OMP_NUM_THREADS", b[11], 1);
+            std::vector<const char*> av = {self, "--mode", child_mode, "--rank", b[0], "--world", b[1], "--device", b[2],
+                                           "--go-fd", b[3], "--out-fd", b[4], "--log2n", b[5], "--n", b[6], "--iters", b[7],
+                                           "--warmup", b[8], "--seconds", b[9], "--seed", b[10], "--dtype", a.dtype.c_str()};
+            if (!a.op.empty()) { av.push_back("--op"); av.push_back(a.op.c_str()); }
+            if (a.inject_fault) av.push_back("--inject-fault");
+            av.push_back(nullptr);
+            execv(self, const_cast<char* const*>(av.data()));
+            _exit(127);
+        }
+        close(go[0]);
+        close(out[1]);
+        kids[r].pid = pid;
+        kids[r].go_w = go[1];
+        kids[r].out_r = out[0];
+        kids[r].res.rank = r;
+    }
+
+    // read READY / RESULT / ERROR lines; release every child at once when all are ready
+    bool released = false;
+    const double deadline = now_s() + timeout_s;
+    int open_pipes = world;
+    while (open_pipes > 0) {
+        std::vector<pollfd> pf;
+        for (auto& k : kids)
+            if (k.out_r >= 0) pf.push_back({k.out_r, POLLIN, 0});
+        const double left = deadline - now_s();
+        if (left <= 0) break;
+        int pr = poll(pf.data(), (nfds_t)pf.size(), (int)std::min(left * 1e3, 1000.0));
+        if (pr < 0 && errno != EINTR) break;
+        for (auto& p : pf) {
+            if (!(p.revents & (POLLIN | POLLHUP))) continue;
+            Child* k = nullptr;
+            for (auto& c : kids)
+                if (c.out_r == p.fd) k = &c;
+            char buf[1024];
+            ssize_t r = read(p.fd, buf, sizeof buf);
+            if (r <= 0) {
+                close(k->out_r);
+                k->out_r = -1;
+                --open_pipes;
+                continue;
+            }
+            k->pending.append(buf, (size_t)r);
+            size_t nl;
+            while ((nl = k->pending.find('\n')) != std::string::npos) {
+                std::string line = k->pending.substr(0, nl);
+                k->pending.erase(0, nl + 1);
+                if (line.rfind("READY", 0) == 0) {
+                    k->ready = true;
+                } else if (line.rfind("NVML", 0) == 0) {
+                    ShardResult& q = k->res;
+                    int rk = 0;
+                    sscanf(line.c_str(), "NVML %d %d %d %lf %llu", &rk, &q.sm_min_mhz, &q.temp_max_c, &q.power_max_w, &q.reasons);
+                } else if (line.rfind("RESULT", 0) == 0) {
+                    ShardResult& s = k->res;
+                    sscanf(line.c_str(), "RESULT %d %d %lf %lf %" SCNu64 " %ld", &s.rank, &s.ok, &s.best_ms, &s.mean_ms, &s.count,
+                           &s.passes);
+                    k->done = true;
+                } else {
+                    k->res.text += line + "\n";
+                }
+            }
+        }
+        if (!released) {
+            bool all = true, any_dead = false;
+            for (auto& k : kids) {
+                all = all && k.ready;
+                any_dead = any_dead || (k.out_r < 0 && !k.ready);
+            }
+            if (all || any_dead) {
+                for (auto& k : kids) {
+                    if (all) {
+                        ssize_t w = write(k.go_w, "g", 1);
+                        (void)w;
+                    }
+                    close(k.go_w);   // closing without a byte tells a waiting child to give up
+                    k.go_w = -1;
+                }
+                released = true;
+            }
+        }
+    }
+    for (auto& k : kids) {
+        if (k.go_w >= 0) close(k.go_w);
+        if (k.out_r >= 0) close(k.out_r);
+        int wst = 0;
+        if (now_s() >= deadline) kill(k.pid, SIGKILL);
+        waitpid(k.pid, &wst, 0);
+        k.res.exit_code = WIFEXITED(wst) ? WEXITSTATUS(wst) : EX_CUDA;
+        results.push_back(k.res);
+    }
+    return EX_PASS;
+}
+
+int mode_node(const Args& a, bool burnin, bool print_verdict)
+{
+    const int visible = probe_device_count();
+    printf("[gpu-validate] %s: one process per GPU, %s\n", burnin ? "burn-in" : "sharded run",
+           burnin ? "every pass verified" : "device-timed, max over ranks");
+    if (visible <= 0) return fail(EX_NO_DEVICE, "no CUDA device is visible to this container");
+    const int world = a.gpus > 0 ? a.gpus : visible;
+    if (world > visible) return fail(EX_NO_DEVICE, "%d GPUs requested, %d visible", world, visible);
+    const int dtype = dtype_id(a.dtype);
+    const int op = a.op.empty() ? B200V_OP_TRIAD : op_id(a.op);
+    Args b = a;
+    if (b.log2n < 0 && !b.n_set) b.log2n = burnin ? 30 : 32;   // configs[3]: 2^32 fp32 elements in total
+    const uint64_t total = b.log2n >= 0 ? (1ull << b.log2n) : b.n;
+    printf("[node] %s %s, %" PRIu64 " elements in total over %d GPU%s (%d visible)\n", op_name(op), a.dtype.c_str(), total, world,
+           world == 1 ? "" : "s", visible);
+    fflush(stdout);
+
+    std::vector<ShardResult> res;
+    int rc = run_children(b, burnin ? "burnin-child" : "shard-child", world, res, 600.0 + 4 * a.seconds);
+    if (rc != EX_PASS) return rc;
+
+    bool ok = true, throttled = false;
+    double max_best = 0, max_mean = 0;
+    uint64_t elems = 0;
+    int worst_exit = EX_PASS;
+    for (auto& s : res) {
+        const bool good = s.exit_code == EX_PASS && s.ok == 1;
+        ok = ok && good;
+        if (s.exit_code != EX_PASS && worst_exit == EX_PASS) worst_exit = s.exit_code;
+        const double bytes = (double)b200v_op_bytes(op, dtype, (size_t)s.count);
+        printf("  rank %d (GPU %d): %" PRIu64 " elements, best %.4f ms (%.1f GB/s), mean %.4f ms, %ld passes, %s\n", s.rank, s.rank,
+               s.count, s.best_ms, s.best_ms > 0 ? bytes / s.best_ms * 1e-6 : 0.0, s.mean_ms, s.passes,
+               good ? "verified" : "FAILED");
+        if (s.temp_max_c >= 0) {
+            const bool bad = (s.reasons & nvmlprobe::kBadReasons) != 0;
+            printf("          under load: SM clock down to %d MHz, up to %d C, up to %.0f W, clock limits seen: %s%s\n", s.sm_min_mhz,
+                   s.temp_max_c, s.power_max_w, nvmlprobe::reasons_text(s.reasons).c_str(),
+                   bad ? "  <-- WARNING: thermal or hardware slowdown" : "");
+            throttled = throttled || bad;
+        }
+        if (!s.text.empty()) printf("%s", s.text.c_str());
+        max_best = std::max(max_best, s.best_ms);
+        max_mean = std::max(max_mean, s.mean_ms);
+        elems += s.count;
+    }
+    double node_gbs = 0;
+    if (max_best > 0) {
+        const double bytes = (double)b200v_op_bytes(op, dtype, (size_t)elems);
+        node_gbs = bytes / max_best * 1e-6;
+        printf("[node] %d GPU%s: %.1f GB/s (bytes / max over ranks of best ms = %.4f), %.1f GB/s sustained (max mean ms = %.4f)\n",
+               world, world == 1 ? "" : "s", node_gbs, max_best, bytes / max_mean * 1e-6, max_mean);
+        printf("[node] per GPU %.1f GB/s = %.1f%% of the %.0f GB/s nominal HBM peak\n", node_gbs / world,
+               100.0 * node_gbs / world / kNominalGBs, kNominalGBs);
+    }
+    if (!a.json_path.empty()) {
+        if (FILE* js = fopen(a.json_path.c_str(), "w")) {
+            fprintf(js, "{\"mode\": \"%s\", \"op\": \"%s\", \"dtype\": \"%s\", \"gpus\": %d, \"elements\": %" PRIu64
+                        ", \"max_best_ms\": %.6f, \"max_mean_ms\": %.6f, \"node_gbs\": %.1f, \"ok\": %s, \"ranks\": [",
+                    burnin ? "burnin" : "node", op_name(op), a.dtype.c_str(), world, elems, max_best, max_mean, node_gbs,
+                    ok ? "true" : "false");
+            for (size_t i = 0; i < res.size(); ++i)
+                fprintf(js, "%s{\"rank\": %d, \"ok\": %d, \"best_ms\": %.6f, \"mean_ms\": %.6f, \"elements\": %" PRIu64 ", \"passes\": %ld, "
+                            "\"sm_min_mhz\": %d, \"temp_max_c\": %d, \"power_max_w\": %.1f, \"clock_limit_reasons\": \"%s\"}",
+                        i ? ", " : "", res[i].rank, res[i].ok, res[i].best_ms, res[i].mean_ms, res[i].count, res[i].passes,
+                        res[i].sm_min_mhz, res[i].temp_max_c, res[i].power_max_w,
+                        res[i].temp_max_c >= 0 ? nvmlprobe::reasons_text(res[i].reasons).c_str() : "unavailable");
+            fprintf(js, "]}\n");
+            fclose(js);
+        }
+    }
+    if (!ok) return fail(worst_exit == EX_PASS ? EX_MISMATCH : worst_exit, "at least one rank failed");
+    if (throttled && a.fail_on_throttle)
+        return fail(EX_MISMATCH, "a GPU reported thermal or hardware slowdown under load (--fail-on-throttle)");
+    return print_verdict ? pass() : EX_PASS;
+}
+
+}  // namespace gpuvalidate
