@@ -88,7 +88,7 @@ def test_op_bytes(L):
 def _gpu_visible():
     try:
         return pkg.device_count() > 0
-    except pkg.B200VError:
+    except Exception:
         return False
 
 
