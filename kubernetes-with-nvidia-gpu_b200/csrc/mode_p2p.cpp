@@ -81,10 +81,12 @@ int mode_p2p(const Args& a, bool print_verdict)
             fflush(stdout);
         }
     }
-    // All GPUs at once: in round k every GPU j pulls from GPU (j+k) mod g, so every NVLink port is
-    // busy in both directions and the switch carries g concurrent flows.  Kernels on different GPUs
-    // are independent (nobody waits on anybody); time = max over GPUs of the device-timed pull.
-    std::vector<double> ring_gbs;
+    // All GPUs at once: in round k every GPU j receives from GPU (j+k) mod g, so every NVLink port is
+    // busy in both directions and the switch carries g concurrent flows.  Two ways of moving the data:
+    // "pull" = a kernel on the destination loads from the peer; "push" = cudaMemcpyPeerAsync issued on
+    // the source's copy engine.  Kernels and copies on different GPUs are independent (nobody waits on
+    // anybody); time = max over GPUs of the device-timed transfer.
+    std::vector<double> ring_gbs, ring_push_gbs;
     {
         std::vector<void*> e0((size_t)g), e1((size_t)g);
         for (int j = 0; j < g; ++j) {
@@ -92,41 +94,50 @@ int mode_p2p(const Args& a, bool print_verdict)
             TRY(b200v_event_create(&e0[j]));
             TRY(b200v_event_create(&e1[j]));
         }
-        printf("  concurrent rounds (every GPU pulls from its k-th neighbour at the same time):\n");
+        printf("  concurrent rounds (every GPU receives from its k-th neighbour at the same time):\n");
         for (int k = 1; k < g; ++k) {
-            double worst = 0;
+            double per_gpu[2] = {0, 0};
             bool round_ok = true;
-            for (int rep = 0; rep < 3; ++rep) {
+            for (int method = 0; method < 2; ++method) {
+                double best = 0;
+                for (int rep = 0; rep < 3; ++rep) {
+                    // owner = the GPU that issues and times the transfer (its events live there):
+                    // the destination for a pull, the source for a push
+                    for (int owner = 0; owner < g; ++owner) {
+                        const int j = method == 0 ? owner : (owner - k + g) % g;   // destination
+                        const int i = (j + k) % g;                                 // source
+                        TRY(b200v_set_device(owner));
+                        TRY(b200v_event_record(e0[owner], nullptr));
+                        if (method == 0) TRY(b200v_peer_pull(dst[j], src[i], bytes, nullptr));
+                        else TRY(b200v_peer_copy(dst[j], j, src[i], i, bytes, nullptr));
+                        TRY(b200v_event_record(e1[owner], nullptr));
+                    }
+                    double slowest = 0;
+                    for (int owner = 0; owner < g; ++owner) {
+                        TRY(b200v_set_device(owner));
+                        TRY(b200v_event_sync(e1[owner]));
+                        float ms = 0;
+                        TRY(b200v_event_elapsed_ms(e0[owner], e1[owner], &ms));
+                        slowest = std::max(slowest, (double)ms);
+                    }
+                    if (rep == 0 || slowest < best) best = slowest;   // best repetition, slowest GPU within it
+                }
                 for (int j = 0; j < g; ++j) {
                     TRY(b200v_set_device(j));
-                    TRY(b200v_event_record(e0[j], nullptr));
-                    TRY(b200v_peer_pull(dst[j], src[(j + k) % g], bytes, nullptr));
-                    TRY(b200v_event_record(e1[j], nullptr));
+                    uint64_t got[2];
+                    TRY(device_checksum(scratch[j], dst[j], bytes, 0, got));
+                    const int i = (j + k) % g;
+                    round_ok = round_ok && got[0] == want[2 * i] && got[1] == want[2 * i + 1];
+                    TRY(b200v_memset(dst[j], 0xEE, bytes, nullptr));
+                    TRY(b200v_device_sync());
                 }
-                double slowest = 0;
-                for (int j = 0; j < g; ++j) {
-                    TRY(b200v_set_device(j));
-                    TRY(b200v_event_sync(e1[j]));
-                    float ms = 0;
-                    TRY(b200v_event_elapsed_ms(e0[j], e1[j], &ms));
-                    slowest = std::max(slowest, (double)ms);
-                }
-                if (rep == 0 || slowest < worst) worst = slowest;   // best of the repetitions, slowest GPU in each
+                per_gpu[method] = bytes / best * 1e-6;
             }
-            for (int j = 0; j < g; ++j) {
-                TRY(b200v_set_device(j));
-                uint64_t got[2];
-                TRY(device_checksum(scratch[j], dst[j], bytes, 0, got));
-                const int i = (j + k) % g;
-                round_ok = round_ok && got[0] == want[2 * i] && got[1] == want[2 * i + 1];
-                TRY(b200v_memset(dst[j], 0xEE, bytes, nullptr));
-                TRY(b200v_device_sync());
-            }
-            const double per_gpu = bytes / worst * 1e-6;
-            ring_gbs.push_back(per_gpu);
+            ring_gbs.push_back(per_gpu[0]);
+            ring_push_gbs.push_back(per_gpu[1]);
             ok = ok && round_ok;
-            printf("    shift %d: %.1f GB/s into every GPU at once (%.1f GB/s through the switch)  %s\n", k, per_gpu, per_gpu * g,
-                   round_ok ? "ok" : "FAILED");
+            printf("    shift %d: pull %.1f, push %.1f GB/s into every GPU at once (%.1f / %.1f GB/s through the switch)  %s\n", k,
+                   per_gpu[0], per_gpu[1], per_gpu[0] * g, per_gpu[1] * g, round_ok ? "ok" : "FAILED");
             fflush(stdout);
         }
         for (int j = 0; j < g; ++j) {
@@ -142,7 +153,8 @@ int mode_p2p(const Args& a, bool print_verdict)
     };
     summary("memcpyPeer", copy_gbs);
     summary("peer-load", pull_gbs);
-    if (!ring_gbs.empty()) summary("concurrent", ring_gbs);
+    if (!ring_gbs.empty()) summary("all pull", ring_gbs);
+    if (!ring_push_gbs.empty()) summary("all push", ring_push_gbs);
     if (!a.json_path.empty()) {
         if (FILE* js = fopen((a.json_path + (a.mode == "full" ? ".p2p" : "")).c_str(), "w")) {
             fprintf(js, "{\"mode\": \"p2p\", \"gpus\": %d, \"bytes\": %zu, \"ok\": %s, \"pairs\": [", g, bytes, ok ? "true" : "false");
@@ -156,6 +168,8 @@ int mode_p2p(const Args& a, bool print_verdict)
                     }
             fprintf(js, "], \"concurrent_shift_gbs_per_gpu\": [");
             for (size_t q = 0; q < ring_gbs.size(); ++q) fprintf(js, "%s%.1f", q ? ", " : "", ring_gbs[q]);
+            fprintf(js, "], \"concurrent_shift_push_gbs_per_gpu\": [");
+            for (size_t q = 0; q < ring_push_gbs.size(); ++q) fprintf(js, "%s%.1f", q ? ", " : "", ring_push_gbs[q]);
             fprintf(js, "]}\n");
             fclose(js);
         }

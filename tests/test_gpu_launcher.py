@@ -142,6 +142,7 @@ def test_p2p_all_pairs(exe, tmp_path):
     assert d["ok"] and len(d["pairs"]) == g * (g - 1)
     assert all(p["memcpy_peer_gbs"] > 100 and p["peer_load_gbs"] > 100 for p in d["pairs"]), d["pairs"]
     assert len(d["concurrent_shift_gbs_per_gpu"]) == g - 1 and min(d["concurrent_shift_gbs_per_gpu"]) > 100
+    assert len(d["concurrent_shift_push_gbs_per_gpu"]) == g - 1 and min(d["concurrent_shift_push_gbs_per_gpu"]) > 100
     assert "concurrent rounds" in r.stdout
 
 
