@@ -88,11 +88,13 @@ int mode_p2p(const Args& a, bool print_verdict)
     // anybody); time = max over GPUs of the device-timed transfer.
     std::vector<double> ring_gbs, ring_push_gbs;
     {
-        std::vector<void*> e0((size_t)g), e1((size_t)g);
+        // one non-blocking stream per GPU: the legacy default stream would couple the devices' queues
+        std::vector<void*> e0((size_t)g), e1((size_t)g), strm((size_t)g);
         for (int j = 0; j < g; ++j) {
             TRY(b200v_set_device(j));
             TRY(b200v_event_create(&e0[j]));
             TRY(b200v_event_create(&e1[j]));
+            TRY(b200v_stream_create(&strm[j]));
         }
         printf("  concurrent rounds (every GPU receives from its k-th neighbour at the same time):\n");
         for (int k = 1; k < g; ++k) {
@@ -107,10 +109,10 @@ int mode_p2p(const Args& a, bool print_verdict)
                         const int j = method == 0 ? owner : (owner - k + g) % g;   // destination
                         const int i = (j + k) % g;                                 // source
                         TRY(b200v_set_device(owner));
-                        TRY(b200v_event_record(e0[owner], nullptr));
-                        if (method == 0) TRY(b200v_peer_pull(dst[j], src[i], bytes, nullptr));
-                        else TRY(b200v_peer_copy(dst[j], j, src[i], i, bytes, nullptr));
-                        TRY(b200v_event_record(e1[owner], nullptr));
+                        TRY(b200v_event_record(e0[owner], strm[owner]));
+                        if (method == 0) TRY(b200v_peer_pull(dst[j], src[i], bytes, strm[owner]));
+                        else TRY(b200v_peer_copy(dst[j], j, src[i], i, bytes, strm[owner]));
+                        TRY(b200v_event_record(e1[owner], strm[owner]));
                     }
                     double slowest = 0;
                     for (int owner = 0; owner < g; ++owner) {
@@ -144,6 +146,7 @@ int mode_p2p(const Args& a, bool print_verdict)
             b200v_set_device(j);
             b200v_event_destroy(e0[j]);
             b200v_event_destroy(e1[j]);
+            b200v_stream_destroy(strm[j]);
         }
     }
     auto summary = [&](const char* name, std::vector<double> v) {
