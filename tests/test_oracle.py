@@ -126,3 +126,30 @@ def test_config0_vector_add_contract_on_host():
     assert L.oracle_vector_add_selftest(50_000, 20261106, 49_999) == 1
     assert L.oracle_vector_add_selftest(1, 1, -1) == 0
     assert L.oracle_vector_add_selftest(0, 1, -1) == 0
+
+
+def test_oracle_under_sanitizers():
+    """The oracle's C sources under AddressSanitizer + UBSan (oracle/selftest.c): ragged sizes on
+    exact-size heap blocks, serial and threaded.  The sanitized build must run clean and print what the
+    plain build prints; spot lines are re-derived through the ctypes view."""
+    import subprocess
+    odir = O.ORACLE_DIR
+    r = subprocess.run(["make", "-C", odir, "sanitize"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    env = dict(os.environ, ASAN_OPTIONS="detect_leaks=1:abort_on_error=0", UBSAN_OPTIONS="print_stacktrace=1", OMP_NUM_THREADS="3")
+    plain = subprocess.run([os.path.join(odir, "selftest")], capture_output=True, text=True, env=env, timeout=300)
+    san = subprocess.run([os.path.join(odir, "selftest_san")], capture_output=True, text=True, env=env, timeout=600)
+    assert plain.returncode == 0 and san.returncode == 0, san.stderr[-3000:]
+    assert "ERROR" not in san.stderr and "runtime error" not in san.stderr, san.stderr[-3000:]
+    assert plain.stdout == san.stdout and plain.stdout.strip().endswith("selftest 0 1 0")
+    lines = plain.stdout.splitlines()
+    assert len(lines) == 3 * 6 * 2 * 8 + 1
+    n, s = 100003, -0.333251953125
+    x = O.fill("f32", (1 << 32) - 5, n, 7, 0, O.GEN_BITS)
+    y = O.fill("f32", (1 << 32) - 5, n, 7, 1, O.GEN_BITS)
+    c = O.checksum(O.op("triad", "f32", n, s=s, x=x, y=y), 3)
+    assert f"triad f32 mode=1 n={n} {c[0]:016x}:{c[1]:016x}" in lines
+    hx = O.fill("bf16", 11, n, 7, 0, O.GEN_DENORM)
+    hy = O.fill("bf16", 11, n, 7, 1, O.GEN_DENORM)
+    c = O.checksum(O.op("add", "bf16", n, x=hx, y=hy), 3)
+    assert f"add bf16 mode=2 n={n} {c[0]:016x}:{c[1]:016x}" in lines
