@@ -253,6 +253,7 @@ void usage()
             "                    [--device D] [--gpus G] [--n N | --log2n K] [--dtype f32|bf16] [--op add|copy|scale|triad]\n"
             "                    [--iters I] [--warmup W] [--seconds S] [--seed X] [--p2p-bytes B]\n"
             "                    [--min-log2-bytes a --max-log2-bytes b] [--measured-copy-gbs G] [--json FILE] [--inject-fault] [--fail-on-throttle]\n"
+            "                    [--hbm-fraction F]   (burnin/full: arrays cover F of each GPU's free HBM instead of --log2n)\n"
             "no arguments: vectorAdd N=50000 on GPU 0, prints Test PASSED / Test FAILED, exit code 0 / non-zero\n");
 }
 
@@ -281,6 +282,7 @@ bool parse(int argc, char** argv, Args& a)
         else if (k == "--iters") a.iters = atoi(v);
         else if (k == "--warmup") a.warmup = atoi(v);
         else if (k == "--seconds") a.seconds = atof(v);
+        else if (k == "--hbm-fraction") a.hbm_fraction = atof(v);
         else if (k == "--seed") a.seed = (uint32_t)strtoul(v, nullptr, 10);
         else if (k == "--p2p-bytes") a.p2p_bytes = strtoull(v, nullptr, 10);
         else if (k == "--min-log2-bytes") a.min_log2_bytes = atoi(v);
@@ -295,6 +297,7 @@ bool parse(int argc, char** argv, Args& a)
     }
     if (a.dtype != "f32" && a.dtype != "bf16") return false;
     if (!a.op.empty() && a.op != "add" && a.op != "copy" && a.op != "scale" && a.op != "triad") return false;
+    if (a.hbm_fraction < 0 || a.hbm_fraction > 0.97) return false;
     if (a.iters < 1 || a.warmup < 0 || a.log2n > 40 || a.min_log2_bytes < 4 || a.max_log2_bytes > 40 ||
         a.min_log2_bytes > a.max_log2_bytes || a.world < 1 || a.rank < 0 || a.rank >= a.world)
         return false;

@@ -48,6 +48,7 @@ struct Args {
     uint32_t seed = 20261106u;
     bool inject_fault = false;
     bool fail_on_throttle = false;   // burn-in: thermal / hardware slowdown reasons fail the run
+    double hbm_fraction = 0.0;       // burn-in: size the three arrays to this share of each GPU's free HBM
     uint64_t p2p_bytes = 1ull << 30;
     int min_log2_bytes = 20, max_log2_bytes = 34;
     double measured_copy_gbs = 0.0;   // optional second denominator (--measured-copy-gbs)

@@ -66,6 +66,19 @@ int mode_shard_child(const Args& a)
     const uint64_t total = a.log2n >= 0 ? (1ull << a.log2n) : a.n;
     uint64_t begin = 0, count = 0;
     CTRY(b200v_shard_range(total, a.rank, a.world, &begin, &count));
+    const bool whole_hbm = burnin && a.hbm_fraction > 0;
+    if (whole_hbm) {
+        // memory-coverage burn-in: the three arrays take the requested share of this GPU's free HBM
+        // (tens of billions of elements: every index computation in the kernels runs past 2^32)
+        b200v_device_info fi;
+        memset(&fi, 0, sizeof fi);
+        fi.struct_size = sizeof fi;
+        CTRY(b200v_device_info_get(a.device, &fi));
+        count = (uint64_t)((double)fi.hbm_free_bytes * a.hbm_fraction / 3.0 / (double)esize(dtype));
+        count &= ~(((uint64_t)1 << 20) - 1);
+        if (count == 0) return child_fail(a, B200V_ERR_NOMEM, "no free HBM to cover");
+        begin = (uint64_t)a.rank * count;   // every rank gets its own stretch of the generator's index space
+    }
     if (dtype == B200V_BF16 && (begin & 1)) {   // keep bf16 shards on 32-bit word boundaries
         begin += 1;
         count -= count ? 1 : 0;
@@ -80,7 +93,9 @@ int mode_shard_child(const Args& a)
     CTRY(b200v_device_sync());
 
     // expected checksums from the host loop (word indices are shard-local)
-    const int nscal = burnin ? 4 : 1;
+    // whole-HBM runs keep to one scalar (the host's expected checksum over ~10^10 elements is the slow part)
+    // and scrub the output between passes instead, so a stale result still cannot pass
+    const int nscal = burnin && !whole_hbm ? 4 : 1;
     uint64_t want[4][2];
     for (int k = 0; k < nscal; ++k)
         hostcheck::expected_checksum(op, dtype, begin, count, a.seed, hostcheck::UNIT, kScalars[k], 0, want[k]);
@@ -136,7 +151,8 @@ int mode_shard_child(const Args& a)
                 }
                 next_probe = now_s() + 0.2;
             }
-            const int k = (int)(passes % 4);
+            const int k = (int)(passes % nscal);
+            if (whole_hbm) CTRY(b200v_memset(v.d, 0x5A, bytes, nullptr));
             CTRY(b200v_event_record(e0, nullptr));
             CTRY(b200v_stream_op(op, dtype, v.d, v.x, two ? v.y : nullptr, kScalars[k], count, nullptr));
             CTRY(b200v_event_record(e1, nullptr));
@@ -233,10 +249,11 @@ int run_children(const Args& a, const char* child_mode, int world, std::vector<S
             snprintf(b[9], 64, "%.3f", a.seconds);
             snprintf(b[10], 64, "%u", a.seed);
             snprintf(b[11], 64, "%d", threads);
+            snprintf(b[12], 64, "%.4f", a.hbm_fraction);
             setenv("OMP_NUM_THREADS", b[11], 1);
             std::vector<const char*> av = {self, "--mode", child_mode, "--rank", b[0], "--world", b[1], "--device", b[2],
                                            "--go-fd", b[3], "--out-fd", b[4], "--log2n", b[5], "--n", b[6], "--iters", b[7],
-                                           "--warmup", b[8], "--seconds", b[9], "--seed", b[10], "--dtype", a.dtype.c_str()};
+                                           "--warmup", b[8], "--seconds", b[9], "--seed", b[10], "--hbm-fraction", b[12], "--dtype", a.dtype.c_str()};
             if (!a.op.empty()) { av.push_back("--op"); av.push_back(a.op.c_str()); }
             if (a.inject_fault) av.push_back("--inject-fault");
             av.push_back(nullptr);
@@ -341,8 +358,12 @@ int mode_node(const Args& a, bool burnin, bool print_verdict)
     Args b = a;
     if (b.log2n < 0 && !b.n_set) b.log2n = burnin ? 30 : 32;   // configs[3]: 2^32 fp32 elements in total
     const uint64_t total = b.log2n >= 0 ? (1ull << b.log2n) : b.n;
-    printf("[node] %s %s, %" PRIu64 " elements in total over %d GPU%s (%d visible)\n", op_name(op), a.dtype.c_str(), total, world,
-           world == 1 ? "" : "s", visible);
+    if (burnin && a.hbm_fraction > 0)
+        printf("[node] %s %s over %.0f%% of each GPU's free HBM, %d GPU%s (%d visible)\n", op_name(op), a.dtype.c_str(),
+               100.0 * a.hbm_fraction, world, world == 1 ? "" : "s", visible);
+    else
+        printf("[node] %s %s, %" PRIu64 " elements in total over %d GPU%s (%d visible)\n", op_name(op), a.dtype.c_str(), total,
+               world, world == 1 ? "" : "s", visible);
     fflush(stdout);
 
     std::vector<ShardResult> res;

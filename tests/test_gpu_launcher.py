@@ -106,6 +106,17 @@ def test_burnin_mode_verifies_every_pass(exe, tmp_path):
     assert "under load: SM clock down to" in r.stdout
 
 
+def test_burnin_over_half_the_hbm(exe, tmp_path):
+    """Memory-coverage burn-in: three arrays over 50 % of free HBM — more than 2^32 elements per array,
+    so every index in the kernels, the fill and the checksum runs past 32 bits — verified against the host loop."""
+    js = tmp_path / "burn.json"
+    r = run(exe, "--mode", "burnin", "--gpus", "1", "--hbm-fraction", "0.5", "--seconds", "2", "--json", str(js))
+    assert r.returncode == 0 and last_line(r) == "Test PASSED", r.stdout + r.stderr
+    d = json.load(open(js))
+    assert d["ok"] and d["ranks"][0]["elements"] > (1 << 32) and d["ranks"][0]["passes"] >= 2
+    assert "50% of each GPU's free HBM" in r.stdout
+
+
 def test_too_many_gpus_requested(exe):
     r = run(exe, "--mode", "node", "--gpus", str(ngpus() + 1), "--log2n", "20")
     assert r.returncode == 2 and last_line(r) == "Test FAILED"
