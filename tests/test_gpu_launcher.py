@@ -90,6 +90,13 @@ def test_node_mode_one_gpu(exe, tmp_path):
     assert d["ok"] and d["gpus"] == 1 and d["elements"] == 1 << 28 and d["node_gbs"] > 4000
 
 
+@pytest.mark.parametrize("op,dtype", [("add", "bf16"), ("copy", "f32"), ("scale", "bf16"), ("triad", "bf16")])
+def test_node_mode_other_ops(exe, op, dtype):
+    r = run(exe, "--mode", "node", "--gpus", "1", "--log2n", "26", "--iters", "3", "--op", op, "--dtype", dtype)
+    assert r.returncode == 0 and last_line(r) == "Test PASSED", r.stdout + r.stderr
+    assert f"[node] {op} {dtype}," in r.stdout and "verified" in r.stdout
+
+
 def test_node_mode_fault_injection(exe):
     r = run(exe, "--mode", "node", "--gpus", "1", "--log2n", "24", "--iters", "2", "--inject-fault")
     assert r.returncode == 1 and last_line(r) == "Test FAILED"
