@@ -116,6 +116,18 @@ int print_devices(int* count_out, bool all_details)
                    nv.sm_max_mhz, nv.mem_mhz, nv.temp_c, nv.power_w, nv.power_limit_w, nvmlprobe::reasons_text(nv.reasons).c_str());
         else if (d == 0 && all_details)
             printf("         (NVML not loadable in this container: no live clocks / temperature / power)\n");
+        nvmlprobe::Health hl;
+        if (all_details && nvmlprobe::health(info.pci_bus_id, &hl)) {
+            printf("         PCIe gen %d x%d (max gen %d x%d)%s", hl.pcie_gen, hl.pcie_width, hl.pcie_gen_max, hl.pcie_width_max,
+                   hl.pcie_width >= 0 && hl.pcie_width < hl.pcie_width_max ? "  <-- WARNING: link is narrower than the slot allows" : "");
+            if (hl.nvlinks_total >= 0)
+                printf(", NVLink %d of %d links up%s", hl.nvlinks_active, hl.nvlinks_total,
+                       hl.nvlinks_active < hl.nvlinks_total ? "  <-- WARNING: links down" : "");
+            if (hl.ecc_uncorrected >= 0)
+                printf(", ECC since driver load: %lld corrected, %lld uncorrected%s", hl.ecc_corrected, hl.ecc_uncorrected,
+                       hl.ecc_uncorrected > 0 ? "  <-- WARNING" : "");
+            printf("\n");
+        }
     }
     if (all_details) b200v_set_device(0);
     if (all_details && count > 1) {

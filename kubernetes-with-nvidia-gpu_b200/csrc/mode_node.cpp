@@ -20,6 +20,7 @@ struct ShardResult {
     int sm_min_mhz = -1, temp_max_c = -1;
     double power_max_w = -1;
     unsigned long long reasons = 0;
+    long long ecc_corrected_new = -1, ecc_uncorrected_new = -1;   // ECC errors that appeared during the run
 };
 
 void child_say(const Args& a, const char* fmt, ...)
@@ -115,6 +116,7 @@ int mode_shard_child(const Args& a)
     int nv_min_mhz = -1, nv_max_temp = -1;
     double nv_max_power = -1;
     unsigned long long nv_reasons = 0;
+    long long ecc_new[2] = {-1, -1};
     if (!burnin) {
         b200v_timing t;
         memset(&t, 0, sizeof t);
@@ -137,6 +139,8 @@ int mode_shard_child(const Args& a)
         memset(&dinfo, 0, sizeof dinfo);
         dinfo.struct_size = sizeof dinfo;
         const bool have_nvml = b200v_device_info_get(a.device, &dinfo) == B200V_OK && nvmlprobe::available();
+        nvmlprobe::Health h_before;
+        const bool have_health = have_nvml && nvmlprobe::health(dinfo.pci_bus_id, &h_before);
         double next_probe = 0;
         while (now_s() < t_end) {
             if (have_nvml && now_s() >= next_probe) {   // a few readings per second while the GPU is loaded
@@ -170,12 +174,20 @@ int mode_shard_child(const Args& a)
             }
         }
         mean_ms = passes ? sum_ms / passes : 0;
+        nvmlprobe::Health h_after;
+        if (have_health && nvmlprobe::health(dinfo.pci_bus_id, &h_after) && h_before.ecc_uncorrected >= 0 &&
+            h_after.ecc_uncorrected >= 0) {
+            ecc_new[0] = h_after.ecc_corrected - h_before.ecc_corrected;
+            ecc_new[1] = h_after.ecc_uncorrected - h_before.ecc_uncorrected;
+            if (ecc_new[1] > 0) ok = 0;   // memory that produced an uncorrectable error during the burn-in has failed it
+        }
         b200v_event_destroy(e0);
         b200v_event_destroy(e1);
     }
     if (a.inject_fault && a.rank == a.world - 1) ok = 0;
     v.release();
-    if (nv_max_temp >= 0) child_say(a, "NVML %d %d %d %.1f %llu", a.rank, nv_min_mhz, nv_max_temp, nv_max_power, nv_reasons);
+    if (nv_max_temp >= 0)
+        child_say(a, "NVML %d %d %d %.1f %llu %lld %lld", a.rank, nv_min_mhz, nv_max_temp, nv_max_power, nv_reasons, ecc_new[0], ecc_new[1]);
     child_say(a, "RESULT %d %d %.6f %.6f %" PRIu64 " %ld", a.rank, ok, best_ms, mean_ms, count, passes);
     return ok ? EX_PASS : EX_MISMATCH;
 }
@@ -303,7 +315,8 @@ int run_children(const Args& a, const char* child_mode, int world, std::vector<S
                 } else if (line.rfind("NVML", 0) == 0) {
                     ShardResult& q = k->res;
                     int rk = 0;
-                    sscanf(line.c_str(), "NVML %d %d %d %lf %llu", &rk, &q.sm_min_mhz, &q.temp_max_c, &q.power_max_w, &q.reasons);
+                    sscanf(line.c_str(), "NVML %d %d %d %lf %llu %lld %lld", &rk, &q.sm_min_mhz, &q.temp_max_c, &q.power_max_w, &q.reasons,
+                           &q.ecc_corrected_new, &q.ecc_uncorrected_new);
                 } else if (line.rfind("RESULT", 0) == 0) {
                     ShardResult& s = k->res;
                     sscanf(line.c_str(), "RESULT %d %d %lf %lf %" SCNu64 " %ld", &s.rank, &s.ok, &s.best_ms, &s.mean_ms, &s.count,
@@ -388,6 +401,9 @@ int mode_node(const Args& a, bool burnin, bool print_verdict)
                    s.temp_max_c, s.power_max_w, nvmlprobe::reasons_text(s.reasons).c_str(),
                    bad ? "  <-- WARNING: thermal or hardware slowdown" : "");
             throttled = throttled || bad;
+            if (s.ecc_uncorrected_new >= 0)
+                printf("          ECC errors during the run: %lld corrected, %lld uncorrected%s\n", s.ecc_corrected_new, s.ecc_uncorrected_new,
+                       s.ecc_uncorrected_new > 0 ? "  <-- FAILED" : "");
         }
         if (!s.text.empty()) printf("%s", s.text.c_str());
         max_best = std::max(max_best, s.best_ms);

@@ -21,7 +21,15 @@ constexpr unsigned long long kHwSlowdown = 0x8, kSwThermal = 0x20, kHwThermal = 
 constexpr unsigned long long kSwPowerCap = 0x4;
 constexpr unsigned long long kBadReasons = kHwSlowdown | kSwThermal | kHwThermal | kHwPowerBrake;
 
+// link and memory-error state: what a node check wants to know besides clocks
+struct Health {
+    int pcie_gen = -1, pcie_width = -1, pcie_gen_max = -1, pcie_width_max = -1;
+    int nvlinks_active = -1, nvlinks_total = -1;
+    long long ecc_corrected = -1, ecc_uncorrected = -1;    // volatile (since driver load) totals; -1 = not reported
+};
+
 bool available();                                         // dlopen + nvmlInit succeeded (cached)
+bool health(const char* pci_bus_id, Health* out);
 bool sample(const char* pci_bus_id, Sample* out);         // false if the device cannot be read
 std::string reasons_text(unsigned long long mask);        // "sw_power_cap,hw_thermal_slowdown" or "none"
 

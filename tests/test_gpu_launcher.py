@@ -66,6 +66,7 @@ def test_list_mode(exe):
     assert r.returncode == 0
     assert re.search(r"GPU 0: NVIDIA B200 .* 148 SMs", r.stdout)
     assert "GPU-" in r.stdout and "driver API" in r.stdout
+    assert re.search(r"PCIe gen \d x\d+ \(max gen \d x\d+\)", r.stdout) and "ECC since driver load" in r.stdout
     assert re.search(r"now: SM \d+ MHz \(max \d+\), memory \d+ MHz, \d+ C, \d+ W of \d+ W, clock limits:", r.stdout)
 
 
@@ -110,7 +111,7 @@ def test_burnin_mode_verifies_every_pass(exe, tmp_path):
     assert d["ok"] and d["ranks"][0]["passes"] >= 20
     r0 = d["ranks"][0]                      # NVML readings taken while the GPU was loaded
     assert r0["temp_max_c"] > 0 and r0["sm_min_mhz"] > 500 and r0["power_max_w"] > 50, r0
-    assert "under load: SM clock down to" in r.stdout
+    assert "under load: SM clock down to" in r.stdout and "ECC errors during the run: " in r.stdout
 
 
 def test_burnin_over_half_the_hbm(exe, tmp_path):
