@@ -2,7 +2,7 @@
 // CSV table (one row per configuration).  The product's csrc/tuning.h is set from these tables
 // (kept under profiles/).  Not part of the product; builds against the same stream_kernels.cuh.
 //
-//   tools/tune [log2_n=28] [iters=10] [stage=all|shape|hint|tma|scale|small|pdl|bf16|ref]
+//   tools/tune [log2_n=28] [iters=10] [stage=all|shape|hint|tma|tma1|scale|small|pdl|bf16|ref]
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
@@ -132,6 +132,43 @@ template <int OP, int TILE_BYTES, int STAGES, int BLOCK> static void add_tma(con
     g_cfg.push_back(c);
 }
 
+// one tile per CTA (grid = tiles), one shared-memory slot: the register kernel's structure, staged by TMA
+template <int OP, int TILE_BYTES, int BLOCK> static void add_tma_oneshot(const char* stage)
+{
+    Config c;
+    c.stage = stage;
+    c.op = OP; c.vecb = TILE_BYTES / 1024; c.unroll = 1; c.block = BLOCK; c.ldh = -2; c.sth = -2;
+    c.tile_elems = TILE_BYTES / 4;
+    c.smem = -TILE_BYTES * (kReadsY<OP> ? 2 : 1);      // negative: marks the one-shot variant (only grid = tiles is run)
+    auto k = stream_kernel_tma<OP, false, TILE_BYTES, 2, BLOCK>;
+    CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, -c.smem));
+    cudaFuncAttributes fa;
+    CK(cudaFuncGetAttributes(&fa, k));
+    c.regs = fa.numRegs;
+    const int smem = -c.smem;
+    c.launch = [k, smem](unsigned grid, void* d, const void* x, const void* y, float s, size_t n) {
+        k<<<grid, BLOCK, smem>>>(d, x, y, s, n / (TILE_BYTES / 4));
+    };
+    g_cfg.push_back(c);
+}
+
+template <int OP> static void add_tma_oneshot_all(const char* stage)
+{
+    add_tma_oneshot<OP, 4096, 128>(stage);
+    add_tma_oneshot<OP, 4096, 256>(stage);
+    add_tma_oneshot<OP, 8192, 128>(stage);
+    add_tma_oneshot<OP, 8192, 256>(stage);
+    add_tma_oneshot<OP, 8192, 512>(stage);
+    add_tma_oneshot<OP, 16384, 256>(stage);
+    add_tma_oneshot<OP, 16384, 512>(stage);
+    add_tma_oneshot<OP, 16384, 1024>(stage);
+    add_tma_oneshot<OP, 32768, 256>(stage);
+    add_tma_oneshot<OP, 32768, 512>(stage);
+    add_tma_oneshot<OP, 32768, 1024>(stage);
+    add_tma_oneshot<OP, 65536, 512>(stage);
+    add_tma_oneshot<OP, 65536, 1024>(stage);
+}
+
 template <int OP> static void add_tma_all(const char* stage)
 {
     add_tma<OP, 8192, 2, 256>(stage);
@@ -256,6 +293,13 @@ int main(int argc, char** argv)
         add_hints<OP_COPY, 32, 8, 256>("hint");
     }
 
+    if (!strcmp(stage, "tma1")) {
+        add_tma_oneshot_all<OP_ADD>("tma1");
+        add_tma_oneshot_all<OP_TRIAD>("tma1");
+        add_tma_oneshot_all<OP_COPY>("tma1");
+        add_cfg<OP_ADD, 32, 4, 512, LD_DEFAULT, ST_DEFAULT>("regref");
+        add_cfg<OP_COPY, 32, 1, 256, LD_DEFAULT, ST_DEFAULT>("regref");
+    }
     if (all || !strcmp(stage, "tma")) {
         add_tma_all<OP_ADD>("tma");
         add_tma_all<OP_TRIAD>("tma");
@@ -294,11 +338,11 @@ int main(int argc, char** argv)
     const int ctas_modes[] = {0, 1, 2, 4, 8};
     for (const Config& cf : g_cfg) {
         const double bytes = (cf.op == OP_COPY || cf.op == OP_SCALE ? 8.0 : 12.0) * n;
-        if (cf.smem > 0) {   // correctness of the TMA variant against the register kernel, once per config
+        if (cf.smem != 0) {   // correctness of the TMA variant against the register kernel, once per config
             if (!cref) CK(cudaMalloc(&cref, n * 4));
             CK(cudaMemset(c, 0, n * 4));
             CK(cudaMemset(dbad, 0, 8));
-            cf.launch(sms, c, a, b, 3.0f, n);
+            cf.launch(cf.smem < 0 ? (unsigned)(n / cf.tile_elems) : (unsigned)sms, c, a, b, 3.0f, n);
             if (cf.op == OP_ADD) stream_kernel<OP_ADD, false, 32, 4, 512, 0, 0><<<(unsigned)(n / 16384), 512>>>(cref, a, b, 3.0f, n);
             else if (cf.op == OP_TRIAD) stream_kernel<OP_TRIAD, false, 32, 4, 512, 0, 0><<<(unsigned)(n / 16384), 512>>>(cref, a, b, 3.0f, n);
             else stream_kernel<OP_COPY, false, 32, 4, 512, 0, 0><<<(unsigned)(n / 16384), 512>>>(cref, a, b, 3.0f, n);
@@ -317,6 +361,7 @@ int main(int argc, char** argv)
             if (cps > 0) grid = std::min(tiles, (size_t)sms * cps);
             if (cps * cf.block > 2048) continue;
             if (cf.smem > 0 && (cps == 0 || (size_t)cps * (cf.smem + 1024) > 227 * 1024)) continue;
+            if (cf.smem < 0 && cps != 0) continue;
             for (int i = 0; i < 2; ++i) cf.launch((unsigned)grid, c, a, b, 3.0f, n);
             CK(cudaGetLastError());
             float best = 1e30f;
