@@ -352,6 +352,37 @@ def test_full_2p32_triad_one_gpu(L):
     assert tuple(got) == oracle_checksum_chunked("triad", "f32", n, 0, 3.0, chunk=1 << 26)
 
 
+def test_sharding_and_repetition_do_not_change_the_result(L):
+    """Size-independent properties at a BASELINE size (2^28 fp32 triad): running the vector as 3, 5 or 8
+    contiguous shards (ragged, so shard starts land on every alignment path) gives the same bits as one
+    launch (checksum of checksums), and running it again gives the same bits again (idempotence)."""
+    n = 1 << 28
+    vp = C.c_void_p
+    dx, dy, whole, parts = (pkg.DeviceBuffer(4 * n) for _ in range(4))
+    pkg.check(L.b200v_fill(pkg.F32, vp(dx.ptr), 0, n, SEED, 0, O.GEN_BITS, None))
+    pkg.check(L.b200v_fill(pkg.F32, vp(dy.ptr), 0, n, SEED, 1, O.GEN_BITS, None))
+    pkg.check(L.b200v_triad_f32(vp(whole.ptr), -0.75, vp(dx.ptr), vp(dy.ptr), n, None))
+    ref = pkg.checksum(vp(whole.ptr), 4 * n)
+    for world in (3, 5, 8):
+        pkg.check(L.b200v_memset(vp(parts.ptr), 0, 4 * n, None))
+        total = [0, 0]
+        for r in range(world):
+            b, c = pkg.shard_range(n - 3, r, world)          # n-3: ragged shard sizes
+            pkg.check(L.b200v_triad_f32(parts.at(4 * b), -0.75, dx.at(4 * b), dy.at(4 * b), c, None))
+            cs = pkg.checksum(parts.at(4 * b), 4 * c, b)
+            total = [(total[0] + cs[0]) & M64, (total[1] + cs[1]) & M64]
+        b = n - 3                                             # the 3 elements left over
+        pkg.check(L.b200v_triad_f32(parts.at(4 * b), -0.75, dx.at(4 * b), dy.at(4 * b), 3, None))
+        cs = pkg.checksum(parts.at(4 * b), 12, b)
+        total = [(total[0] + cs[0]) & M64, (total[1] + cs[1]) & M64]
+        assert tuple(total) == ref, world
+        assert pkg.checksum(vp(parts.ptr), 4 * n) == ref
+    pkg.check(L.b200v_triad_f32(vp(whole.ptr), -0.75, vp(dx.ptr), vp(dy.ptr), n, None))
+    assert pkg.checksum(vp(whole.ptr), 4 * n) == ref
+    for b in (dx, dy, whole, parts):
+        b.free()
+
+
 def test_time_op_reports_device_times(L):
     n = 1 << 26
     dx, dy, dd = (pkg.DeviceBuffer(n * 4) for _ in range(3))
