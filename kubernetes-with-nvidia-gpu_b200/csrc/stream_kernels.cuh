@@ -168,6 +168,10 @@ stream_kernel(void* __restrict__ dst, const void* __restrict__ x, const void* __
     const V* __restrict__ vx = reinterpret_cast<const V*>(x);
     const V* __restrict__ vy = reinterpret_cast<const V*>(y);
 
+    // (Left to the compiler's default unrolling on purpose.  `#pragma unroll 1` removes the 64-bit
+    // trip-count division nvcc puts in front of the loop, but ptxas then allocates ~58 instead of 80
+    // registers, sinks loads between the stores again, and the kernel loses 1.5 %:
+    // profiles/r01_tune_negative_results.md.)
     for (size_t tile = blockIdx.x; tile < full_tiles; tile += gridDim.x) {
         const size_t base = tile * TILE_VECS + threadIdx.x;
         V a[UNROLL];
@@ -188,8 +192,14 @@ stream_kernel(void* __restrict__ dst, const void* __restrict__ x, const void* __
         }
     }
 
-    if (blockIdx.x == full_tiles % gridDim.x) {
-        const size_t done = full_tiles * TILE_ELEMS;
+    // The remainder belongs to the CTA that would take the next tile.  With one tile per CTA that is
+    // CTA 0 (or the only CTA when there is no full tile); the 64-bit modulo is only evaluated for a
+    // clamped or persistent grid, and nothing at all runs here when n is a whole number of tiles —
+    // a CTA that lives for a few microseconds should not end with a ~100-cycle division.
+    const size_t done = full_tiles * TILE_ELEMS;
+    if (done == n) return;
+    const size_t owner = gridDim.x >= full_tiles ? (gridDim.x == full_tiles ? 0 : full_tiles) : full_tiles % gridDim.x;
+    if (blockIdx.x == owner) {
         if constexpr (!BF16) {
             float* d = reinterpret_cast<float*>(dst);
             const float* fx = reinterpret_cast<const float*>(x);

@@ -2,7 +2,7 @@
 // CSV table (one row per configuration).  The product's csrc/tuning.h is set from these tables
 // (kept under profiles/).  Not part of the product; builds against the same stream_kernels.cuh.
 //
-//   tools/tune [log2_n=28] [iters=10] [stage=all|shape|hint|tma|tma1|scale|small|pdl|bf16|ref]
+//   tools/tune [log2_n=28] [iters=10] [stage=all|shape|hint|tma|tma1|scale|small|pdl|bf16|lockstep|ref]
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
@@ -37,6 +37,79 @@ __global__ void init_values(float* p, size_t n, uint32_t salt)
 {
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
         p[i] = (float)((((uint32_t)i ^ salt) * 2654435761u) >> 8) * 0x1p-24f;
+}
+
+// Experiment for DESIGN.md's "persistent CTAs run in lock-step" reading: the product's main loop as a
+// persistent grid, optionally with every CTA starting after its own short delay (0 .. 6.3 us).
+// Occupancy probe: the one-tile body with PAD registers held live across it (read from %clock at entry,
+// "used" at exit), so the resident CTAs per SM can be dialled through the register file alone — no shared
+// memory request (which would shrink L1), no change to the memory instructions.
+template <int OP, int UNROLL, int BLOCK, int PAD>
+__global__ void __launch_bounds__(BLOCK)
+occupancy_probe_kernel(void* __restrict__ dst, const void* __restrict__ x, const void* __restrict__ y, float s, size_t n)
+{
+    using V = Vec<32>;
+    constexpr size_t TILE_VECS = (size_t)BLOCK * UNROLL;
+    const size_t full_tiles = n / (TILE_VECS * 8);
+    uint32_t pad[PAD > 0 ? PAD : 1];
+#pragma unroll
+    for (int i = 0; i < PAD; ++i) asm volatile("mov.u32 %0, %%clock;" : "=r"(pad[i]));
+    V* vd = reinterpret_cast<V*>(dst);
+    const V* vx = reinterpret_cast<const V*>(x);
+    const V* vy = reinterpret_cast<const V*>(y);
+    uint32_t last = 0;
+#pragma unroll 1
+    for (size_t tile = blockIdx.x; tile < full_tiles; tile += gridDim.x) {
+        const size_t base = tile * TILE_VECS + threadIdx.x;
+        V a[UNROLL], b[UNROLL];
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) a[u] = ldg<LD_DEFAULT>(vx + base + (size_t)u * BLOCK);
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) b[u] = ldg<LD_DEFAULT>(vy + base + (size_t)u * BLOCK);
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) {
+            V r;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) r.w[k] = op_word<OP, false>(a[u].w[k], b[u].w[k], s);
+            stg<ST_DEFAULT>(vd + base + (size_t)u * BLOCK, r);
+            last = r.w[0];
+        }
+    }
+    // a chain that needs every pad register after the last loaded value is known keeps them all live
+    if (PAD > 0) {
+        uint32_t acc = last;
+#pragma unroll
+        for (int i = 0; i < PAD; ++i) acc = acc * pad[i] + 1u;
+        if (acc == 0xDEADBEEFu) reinterpret_cast<uint32_t*>(dst)[0] = acc;
+    }
+}
+
+template <int OP, int UNROLL, int BLOCK, bool STAGGER>
+__global__ void __launch_bounds__(BLOCK)
+persistent_probe_kernel(void* __restrict__ dst, const void* __restrict__ x, const void* __restrict__ y, float s, size_t n)
+{
+    using V = Vec<32>;
+    constexpr size_t TILE_VECS = (size_t)BLOCK * UNROLL;
+    const size_t full_tiles = n / (TILE_VECS * 8);
+    if (STAGGER) __nanosleep(((blockIdx.x * 37u) % 64u) * 100u);
+    V* vd = reinterpret_cast<V*>(dst);
+    const V* vx = reinterpret_cast<const V*>(x);
+    const V* vy = reinterpret_cast<const V*>(y);
+    for (size_t tile = blockIdx.x; tile < full_tiles; tile += gridDim.x) {
+        const size_t base = tile * TILE_VECS + threadIdx.x;
+        V a[UNROLL], b[UNROLL];
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) a[u] = ldg<LD_DEFAULT>(vx + base + (size_t)u * BLOCK);
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) b[u] = ldg<LD_DEFAULT>(vy + base + (size_t)u * BLOCK);
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) {
+            V r;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) r.w[k] = op_word<OP, false>(a[u].w[k], b[u].w[k], s);
+            stg<ST_DEFAULT>(vd + base + (size_t)u * BLOCK, r);
+        }
+    }
 }
 
 struct Config {
@@ -86,6 +159,86 @@ template <int OP> static void add_bf16_shapes(const char* stage)
     add_cfg<OP, 16, 4, 1024, LD_DEFAULT, ST_DEFAULT, true>(stage);
     add_cfg<OP, 32, 4, 512, LD_NC_NA, ST_DEFAULT, true>(stage);
     add_cfg<OP, 32, 2, 512, LD_NC_NA, ST_DEFAULT, true>(stage);
+}
+
+template <int OP, int UNROLL, int BLOCK, bool STAGGER> static void add_probe(const char* stage)
+{
+    Config c;
+    c.stage = stage;
+    c.op = OP; c.vecb = 32; c.unroll = UNROLL; c.block = BLOCK; c.ldh = STAGGER ? 8 : 7; c.sth = 0;   // ld 7 = plain, 8 = staggered
+    c.tile_elems = (size_t)BLOCK * UNROLL * 8;
+    auto k = persistent_probe_kernel<OP, UNROLL, BLOCK, STAGGER>;
+    cudaFuncAttributes fa;
+    CK(cudaFuncGetAttributes(&fa, k));
+    c.regs = fa.numRegs;
+    c.launch = [k](unsigned grid, void* d, const void* x, const void* y, float s, size_t n) { k<<<grid, BLOCK>>>(d, x, y, s, n); };
+    g_cfg.push_back(c);
+}
+
+// the product kernel with its residency capped by a dummy dynamic shared-memory request: st column = CTAs per SM allowed
+template <int OP, int VECB, int UNROLL, int BLOCK> static void add_occ(const char* stage, int ctas)
+{
+    Config c;
+    c.stage = stage;
+    c.op = OP; c.vecb = VECB; c.unroll = UNROLL; c.block = BLOCK; c.ldh = 6; c.sth = ctas;
+    c.tile_elems = (size_t)BLOCK * UNROLL * (VECB / 4);
+    auto k = stream_kernel<OP, false, VECB, UNROLL, BLOCK, LD_DEFAULT, ST_DEFAULT>;
+    const int smem = ctas > 0 ? (227 * 1024 / ctas - 1024) & ~127 : 0;
+    CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    cudaFuncAttributes fa;
+    CK(cudaFuncGetAttributes(&fa, k));
+    c.regs = fa.numRegs;
+    c.launch = [k, smem](unsigned grid, void* d, const void* x, const void* y, float s, size_t n) {
+        k<<<grid, BLOCK, smem>>>(d, x, y, s, n);
+    };
+    g_cfg.push_back(c);
+}
+
+// the product kernel with the L1/shared split moved (no shared memory is used): st column = carve-out percent
+template <int OP, int VECB, int UNROLL, int BLOCK> static void add_carve(const char* stage, int percent)
+{
+    Config c;
+    c.stage = stage;
+    c.op = OP; c.vecb = VECB; c.unroll = UNROLL; c.block = BLOCK; c.ldh = 5; c.sth = percent;
+    c.tile_elems = (size_t)BLOCK * UNROLL * (VECB / 4);
+    auto k = stream_kernel<OP, false, VECB, UNROLL, BLOCK, LD_DEFAULT, ST_DEFAULT>;
+    cudaFuncAttributes fa;
+    CK(cudaFuncGetAttributes(&fa, k));
+    c.regs = fa.numRegs;
+    c.launch = [k, percent](unsigned grid, void* d, const void* x, const void* y, float s, size_t n) {
+        CK(cudaFuncSetAttribute(k, cudaFuncAttributePreferredSharedMemoryCarveout, percent));
+        k<<<grid, BLOCK>>>(d, x, y, s, n);
+    };
+    g_cfg.push_back(c);
+}
+
+template <int OP, int UNROLL, int BLOCK, int PAD> static void add_occprobe(const char* stage)
+{
+    Config c;
+    c.stage = stage;
+    c.op = OP; c.vecb = 32; c.unroll = UNROLL; c.block = BLOCK; c.ldh = 4; c.sth = PAD;   // st column = PAD
+    c.tile_elems = (size_t)BLOCK * UNROLL * 8;
+    auto k = occupancy_probe_kernel<OP, UNROLL, BLOCK, PAD>;
+    cudaFuncAttributes fa;
+    CK(cudaFuncGetAttributes(&fa, k));
+    c.regs = fa.numRegs;
+    c.launch = [k](unsigned grid, void* d, const void* x, const void* y, float s, size_t n) { k<<<grid, BLOCK>>>(d, x, y, s, n); };
+    g_cfg.push_back(c);
+}
+
+template <int OP, int UNROLL, int BLOCK> static void add_occprobe_all(const char* stage)
+{
+    add_occprobe<OP, UNROLL, BLOCK, 0>(stage);
+    add_occprobe<OP, UNROLL, BLOCK, 8>(stage);
+    add_occprobe<OP, UNROLL, BLOCK, 16>(stage);
+    add_occprobe<OP, UNROLL, BLOCK, 24>(stage);
+    add_occprobe<OP, UNROLL, BLOCK, 32>(stage);
+    add_occprobe<OP, UNROLL, BLOCK, 40>(stage);
+    add_occprobe<OP, UNROLL, BLOCK, 56>(stage);
+    add_occprobe<OP, UNROLL, BLOCK, 72>(stage);
+    add_occprobe<OP, UNROLL, BLOCK, 100>(stage);
+    add_occprobe<OP, UNROLL, BLOCK, 140>(stage);
+    add_occprobe<OP, UNROLL, BLOCK, 200>(stage);
 }
 
 // the same register kernel launched with programmatic stream serialization (PDL); ld column = 9
@@ -267,6 +420,65 @@ int main(int argc, char** argv)
         add_cfg<OP_ADD, 32, 4, 512, LD_DEFAULT, ST_DEFAULT>("f32ref");
         add_cfg<OP_TRIAD, 32, 4, 512, LD_DEFAULT, ST_DEFAULT>("f32ref");
         add_cfg<OP_SCALE, 32, 1, 1024, LD_DEFAULT, ST_DEFAULT>("f32ref");
+    }
+    if (!strcmp(stage, "recheck")) {   // the shipped shapes against their neighbours, three interleaved rounds (box noise)
+        for (int round = 0; round < 3; ++round) {
+            add_cfg<OP_ADD, 32, 4, 512, LD_DEFAULT, ST_DEFAULT>("recheck");
+            add_cfg<OP_ADD, 32, 1, 256, LD_DEFAULT, ST_DEFAULT>("recheck");
+            add_cfg<OP_ADD, 32, 2, 256, LD_DEFAULT, ST_DEFAULT>("recheck");
+            add_cfg<OP_ADD, 32, 1, 128, LD_DEFAULT, ST_DEFAULT>("recheck");
+            add_cfg<OP_ADD, 32, 1, 512, LD_DEFAULT, ST_DEFAULT>("recheck");
+            add_cfg<OP_ADD, 32, 2, 512, LD_DEFAULT, ST_DEFAULT>("recheck");
+            add_probe<OP_ADD, 1, 256, false>("probe");
+            add_probe<OP_ADD, 4, 512, false>("probe");
+            add_pdl<OP_ADD, 32, 4, 512>("recheck-pdl");
+            add_pdl<OP_ADD, 32, 1, 256>("recheck-pdl");
+        }
+    }
+    if (!strcmp(stage, "occ")) {
+        for (int ctas : {0, 8, 6, 5, 4, 3, 2, 1}) {
+            add_occ<OP_ADD, 32, 1, 256>("occ", ctas);
+            add_occ<OP_ADD, 32, 2, 256>("occ", ctas);
+            add_occ<OP_ADD, 32, 1, 128>("occ", ctas);
+            add_occ<OP_ADD, 32, 1, 512>("occ", ctas);
+            add_occ<OP_ADD, 32, 2, 512>("occ", ctas);
+            add_occ<OP_ADD, 32, 4, 256>("occ", ctas);
+            add_occ<OP_ADD, 32, 2, 128>("occ", ctas);
+            add_occ<OP_ADD, 32, 4, 128>("occ", ctas);
+            add_occ<OP_COPY, 32, 1, 256>("occ", ctas);
+            add_occ<OP_COPY, 32, 2, 256>("occ", ctas);
+            add_occ<OP_COPY, 32, 4, 256>("occ", ctas);
+        }
+        add_cfg<OP_ADD, 32, 4, 512, LD_DEFAULT, ST_DEFAULT>("occref");
+        add_probe<OP_ADD, 1, 256, false>("probe");
+    }
+    if (!strcmp(stage, "carve")) {
+        for (int pct : {-1, 0, 25, 50, 75, 90, 100}) {
+            add_carve<OP_ADD, 32, 4, 512>("carve", pct);
+            add_carve<OP_ADD, 32, 1, 256>("carve", pct);
+            add_carve<OP_ADD, 32, 2, 512>("carve", pct);
+            add_carve<OP_COPY, 32, 1, 256>("carve", pct);
+            add_carve<OP_SCALE, 32, 1, 1024>("carve", pct);
+        }
+        add_probe<OP_ADD, 1, 256, false>("probe");
+    }
+    if (!strcmp(stage, "occprobe")) {
+        add_occprobe_all<OP_ADD, 1, 256>("occprobe");
+        add_occprobe_all<OP_ADD, 1, 128>("occprobe");
+        add_occprobe_all<OP_ADD, 2, 256>("occprobe");
+        add_occprobe_all<OP_ADD, 2, 128>("occprobe");
+        add_occprobe_all<OP_ADD, 4, 128>("occprobe");
+        add_occprobe_all<OP_ADD, 1, 512>("occprobe");
+        add_occprobe_all<OP_COPY, 1, 256>("occprobe");
+        add_occprobe_all<OP_COPY, 2, 256>("occprobe");
+    }
+    if (!strcmp(stage, "lockstep")) {
+        add_probe<OP_ADD, 4, 512, false>("lockstep");
+        add_probe<OP_ADD, 4, 512, true>("lockstep");
+        add_probe<OP_ADD, 2, 256, false>("lockstep");
+        add_probe<OP_ADD, 2, 256, true>("lockstep");
+        add_probe<OP_ADD, 1, 256, false>("lockstep");
+        add_probe<OP_ADD, 1, 256, true>("lockstep");
     }
     if (!strcmp(stage, "pdl")) {
         add_cfg<OP_ADD, 32, 4, 512, LD_DEFAULT, ST_DEFAULT>("pdl");
