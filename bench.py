@@ -380,6 +380,7 @@ def main():
             "parallelism": f"shard{world} (one process per GPU, no collective on the data path)",
             "l2": f"the three arrays are {3 * nbytes >> 20} MiB per GPU, far larger than the 126 MB L2: no flush between steps",
             "gpu": info.name.decode(), "sm_count": info.sm_count,
+            "inputs": f"index-hash generator, UNIT mode (24-bit k * 2^-24), seed {SEED}, streams 0/1, filled on the device before the timed region",
         },
         "roofline": {
             "bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",

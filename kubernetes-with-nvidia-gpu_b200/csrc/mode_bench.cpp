@@ -9,8 +9,8 @@ namespace gpuvalidate {
 
 int mode_bench(const Args& a)
 {
-    printf("[gpu-validate] STREAM sweep: copy/scale/add/triad, fp32 + bf16, per-array 2^%d..2^%d bytes\n", a.min_log2_bytes,
-           a.max_log2_bytes);
+    printf("[gpu-validate] STREAM sweep: copy/scale/add/triad, fp32 + bf16, per-array 2^%d..2^%d bytes, s = 3.0, seed %u\n",
+           a.min_log2_bytes, a.max_log2_bytes, a.seed);
     int count = 0;
     int st = print_devices(&count, false);
     if (st != B200V_OK) return fail_status(st, "device discovery");

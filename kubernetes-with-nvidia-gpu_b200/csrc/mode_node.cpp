@@ -361,8 +361,8 @@ int run_children(const Args& a, const char* child_mode, int world, std::vector<S
 int mode_node(const Args& a, bool burnin, bool print_verdict)
 {
     const int visible = probe_device_count();
-    printf("[gpu-validate] %s: one process per GPU, %s\n", burnin ? "burn-in" : "sharded run",
-           burnin ? "every pass verified" : "device-timed, max over ranks");
+    printf("[gpu-validate] %s: one process per GPU, %s (seed %u)\n", burnin ? "burn-in" : "sharded run",
+           burnin ? "every pass verified" : "device-timed, max over ranks", a.seed);
     if (visible <= 0) return fail(EX_NO_DEVICE, "no CUDA device is visible to this container");
     const int world = a.gpus > 0 ? a.gpus : visible;
     if (world > visible) return fail(EX_NO_DEVICE, "%d GPUs requested, %d visible", world, visible);
