@@ -127,3 +127,26 @@ def test_pod_manifest_keeps_the_reference_envelope():
     job = yaml.safe_load(open(os.path.join(deploy, "job-node-validate.yaml")))
     jc = job["spec"]["template"]["spec"]["containers"][0]
     assert jc["resources"]["limits"]["nvidia.com/gpu"] == 8 and "--mode" in jc["args"]
+
+
+def test_host_loops_under_sanitizers_and_against_the_oracle():
+    """hostcheck.cpp (the launcher's host reference) under AddressSanitizer + UBSan, and line by line
+    against oracle/selftest: both print `op dtype mode n checksum` for the same seeded cases, and the two
+    independent implementations must print the same lines."""
+    pkg_dir = os.path.join(ROOT, "kubernetes-with-nvidia-gpu_b200")
+    r = subprocess.run(["make", "-C", pkg_dir, "hostcheck-selftest"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    r = subprocess.run(["make", "-C", os.path.join(ROOT, "oracle"), "selftest"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    env = dict(os.environ, OMP_NUM_THREADS="3", ASAN_OPTIONS="detect_leaks=1")
+    plain = subprocess.run([os.path.join(pkg_dir, "hostcheck_selftest")], capture_output=True, text=True, env=env, timeout=300)
+    san = subprocess.run([os.path.join(pkg_dir, "hostcheck_selftest_san")], capture_output=True, text=True, env=env, timeout=600)
+    assert plain.returncode == 0 and san.returncode == 0, san.stderr[-3000:]
+    assert "ERROR" not in san.stderr and "runtime error" not in san.stderr, san.stderr[-3000:]
+    assert plain.stdout == san.stdout and plain.stdout.strip().endswith("hostcheck selftest ok")
+    orc = subprocess.run([os.path.join(ROOT, "oracle", "selftest")], capture_output=True, text=True, env=env, timeout=300)
+    assert orc.returncode == 0
+    ours = {ln for ln in plain.stdout.splitlines() if " mode=" in ln}
+    theirs = {ln for ln in orc.stdout.splitlines() if " mode=" in ln}
+    assert len(ours) == 2 * 3 * 6 * 4 - 0 or len(ours) > 100
+    assert ours == theirs
