@@ -123,7 +123,10 @@ B200V_API int b200v_fill(int dtype, void *d_dst, uint64_t start, size_t n, uint3
  *   add   : c[i] = a[i] + b[i]          (cuda-samples vectorAdd / STREAM add)
  *   copy  : c[i] = a[i]
  *   scale : b[i] = s * c[i]
- *   triad : a[i] = fmaf(s, c[i], b[i])  (one rounding)                                      */
+ *   triad : a[i] = fmaf(s, c[i], b[i])  (one rounding)
+ * Launches carry cudaLaunchAttributeProgrammaticStreamSerialization and the kernels wait
+ * (griddepcontrol.wait) before touching memory: consecutive launches on one stream overlap
+ * their drain/placement, the order of the data on the stream is the usual one.              */
 B200V_API int b200v_add_f32(float *c, const float *a, const float *b, size_t n, void *stream);
 B200V_API int b200v_copy_f32(float *c, const float *a, size_t n, void *stream);
 B200V_API int b200v_scale_f32(float *b, float s, const float *c, size_t n, void *stream);
