@@ -13,6 +13,7 @@
 
 #include "stream_kernels.cuh"
 #include "stream_tma.cuh"
+#include "checksum_kernel.cuh"
 
 using namespace b200v;
 
@@ -239,6 +240,30 @@ template <int OP, int UNROLL, int BLOCK> static void add_occprobe_all(const char
     add_occprobe<OP, UNROLL, BLOCK, 100>(stage);
     add_occprobe<OP, UNROLL, BLOCK, 140>(stage);
     add_occprobe<OP, UNROLL, BLOCK, 200>(stage);
+}
+
+// checksum reduction variants: vecb column = 16, unroll = loads in flight, ld column = 1 if tiled, ctas_per_sm modes apply
+static unsigned int* g_ck_counter = nullptr;
+static uint64_t* g_ck_partials = nullptr;
+static uint64_t* g_ck_out = nullptr;
+template <int UNROLL, bool TILED> static void add_cksum(const char* stage)
+{
+    Config c;
+    c.stage = stage;
+    c.op = OP_COPY;   // 4 bytes read per word: reported through the 8 B/word copy accounting, halved below
+    c.vecb = 16; c.unroll = UNROLL; c.block = kChecksumBlock; c.ldh = TILED ? 1 : 0; c.sth = 0;
+    c.tile_elems = (size_t)kChecksumBlock * UNROLL * 4;
+    auto k = checksum_kernel<UNROLL, TILED>;
+    cudaFuncAttributes fa;
+    CK(cudaFuncGetAttributes(&fa, k));
+    c.regs = fa.numRegs;
+    c.smem = 0;
+    c.launch = [k](unsigned grid, void*, const void* x, const void*, float, size_t n) {
+        if (grid > 2048) grid = 2048;
+        CK(cudaMemsetAsync(g_ck_counter, 0, 16));
+        k<<<grid, kChecksumBlock>>>((const unsigned char*)x, n * 4, 0, g_ck_counter, g_ck_partials, g_ck_out);
+    };
+    g_cfg.push_back(c);
 }
 
 // the same register kernel launched with programmatic stream serialization (PDL); ld column = 9
@@ -471,6 +496,17 @@ int main(int argc, char** argv)
         add_occprobe_all<OP_ADD, 1, 512>("occprobe");
         add_occprobe_all<OP_COPY, 1, 256>("occprobe");
         add_occprobe_all<OP_COPY, 2, 256>("occprobe");
+    }
+    if (!strcmp(stage, "cksum")) {   // GB/s columns count 8 B per word (copy accounting): halve them for the 4 B actually read
+        CK(cudaMalloc(&g_ck_counter, 256));
+        CK(cudaMalloc(&g_ck_partials, 2048 * 16));
+        CK(cudaMalloc(&g_ck_out, 16));
+        add_cksum<4, false>("cksum");
+        add_cksum<8, false>("cksum");
+        add_cksum<2, true>("cksum");
+        add_cksum<4, true>("cksum");
+        add_cksum<8, true>("cksum");
+        add_cksum<16, true>("cksum");
     }
     if (!strcmp(stage, "lockstep")) {
         add_probe<OP_ADD, 4, 512, false>("lockstep");
