@@ -219,6 +219,18 @@ int probe_device_count()
     return r == (ssize_t)sizeof n ? n : -1;
 }
 
+// Pod deletion sends SIGTERM to PID 1: pass it on to the shard children so no GPU process outlives the pod.
+volatile sig_atomic_t g_child_pids[64];
+volatile sig_atomic_t g_child_count = 0;
+
+void forward_signal(int sig)
+{
+    for (int i = 0; i < g_child_count; ++i)
+        if (g_child_pids[i] > 0) kill((pid_t)g_child_pids[i], SIGTERM);
+    signal(sig, SIG_DFL);
+    raise(sig);
+}
+
 struct Child {
     pid_t pid = -1;
     int go_w = -1, out_r = -1;
@@ -235,6 +247,9 @@ int run_children(const Args& a, const char* child_mode, int world, std::vector<S
     self[len] = 0;
 
     std::vector<Child> kids((size_t)world);
+    g_child_count = 0;
+    signal(SIGTERM, forward_signal);
+    signal(SIGINT, forward_signal);
     const int threads = std::max(1, hostcheck::max_threads() / world);
     for (int r = 0; r < world; ++r) {
         int go[2], out[2];
@@ -274,6 +289,10 @@ int run_children(const Args& a, const char* child_mode, int world, std::vector<S
         }
         close(go[0]);
         close(out[1]);
+        if (r < 64) {
+            g_child_pids[r] = (sig_atomic_t)pid;
+            g_child_count = r + 1;
+        }
         kids[r].pid = pid;
         kids[r].go_w = go[1];
         kids[r].out_r = out[0];
@@ -355,6 +374,9 @@ int run_children(const Args& a, const char* child_mode, int world, std::vector<S
         k.res.exit_code = WIFEXITED(wst) ? WEXITSTATUS(wst) : EX_CUDA;
         results.push_back(k.res);
     }
+    g_child_count = 0;
+    signal(SIGTERM, SIG_DFL);
+    signal(SIGINT, SIG_DFL);
     return EX_PASS;
 }
 

@@ -125,6 +125,29 @@ def test_burnin_over_half_the_hbm(exe, tmp_path):
     assert "50% of each GPU's free HBM" in r.stdout
 
 
+def test_sigterm_reaches_the_shard_children(exe):
+    """Deleting the pod sends SIGTERM to the entrypoint: the per-GPU children must go with it."""
+    import signal
+    import time
+
+    import psutil
+    p = subprocess.Popen([exe, "--mode", "burnin", "--gpus", "1", "--log2n", "26", "--seconds", "60"],
+                         stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+    kids = []
+    for _ in range(100):                       # wait for the shard child to exist and start working
+        time.sleep(0.1)
+        kids = psutil.Process(p.pid).children(recursive=True)
+        if kids and any("burnin-child" in " ".join(k.cmdline()) for k in kids):
+            break
+    assert kids, "no shard child was started"
+    time.sleep(1.0)
+    p.send_signal(signal.SIGTERM)
+    p.wait(timeout=15)
+    assert p.returncode != 0
+    gone, alive = psutil.wait_procs(kids, timeout=15)
+    assert not alive, f"children survived the parent: {alive}"
+
+
 def test_too_many_gpus_requested(exe):
     r = run(exe, "--mode", "node", "--gpus", str(ngpus() + 1), "--log2n", "20")
     assert r.returncode == 2 and last_line(r) == "Test FAILED"
