@@ -133,11 +133,21 @@ def test_sigterm_reaches_the_shard_children(exe):
     import psutil
     p = subprocess.Popen([exe, "--mode", "burnin", "--gpus", "1", "--log2n", "26", "--seconds", "60"],
                          stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+    def shard_children():
+        found = []
+        for k in psutil.Process(p.pid).children(recursive=True):
+            try:                               # the short-lived device-count probe may be a zombie by now
+                if "burnin-child" in " ".join(k.cmdline()):
+                    found.append(k)
+            except psutil.Error:
+                pass
+        return found
+
     kids = []
     for _ in range(100):                       # wait for the shard child to exist and start working
         time.sleep(0.1)
-        kids = psutil.Process(p.pid).children(recursive=True)
-        if kids and any("burnin-child" in " ".join(k.cmdline()) for k in kids):
+        kids = shard_children()
+        if kids:
             break
     assert kids, "no shard child was started"
     time.sleep(1.0)
