@@ -154,11 +154,50 @@ __device__ __forceinline__ uint32_t gen_bf16_bits(uint32_t key, uint64_t index, 
     return b;
 }
 
+// The vector body of the fill is integer-ALU bound if written naively (ncu: ALU pipe 95 %, DRAM 48 %).
+// Its fast path therefore (a) takes the generator mode as a template parameter, (b) hoists the
+// high-half term of the hash out of the per-element work (a vector that straddles a 2^32 index
+// boundary takes the plain path), and (c) does every `x >> s` as a multiply-high by 2^(32-s) so the
+// shifts run on the FMA pipe (IMAD.HI) beside the two hash multiplies and leave the ALU pipe the
+// XORs.  The multipliers arrive as kernel arguments so that ptxas cannot turn them back into shifts.
+// Same integer function as mix32/hash32 above, bit for bit (tests/test_gpu_parity.py: fill vs oracle).
+
+struct ShiftMul {
+    uint32_t m16, m17, m24, m8;   // 2^16, 2^17 (>> 15), 2^24 (>> 8), 2^8 (>> 24)
+};
+
+__device__ __forceinline__ uint32_t mix32_fma(uint32_t x, const ShiftMul& m)
+{
+    x ^= __umulhi(x, m.m16);
+    x *= 0x7FEB352Du;
+    x ^= __umulhi(x, m.m17);
+    x *= 0x846CA68Bu;
+    x ^= __umulhi(x, m.m16);
+    return x;
+}
+
+template <int MODE> __device__ __forceinline__ uint32_t f32_from_hash(uint32_t h, const ShiftMul& m)
+{
+    if constexpr (MODE == B200V_GEN_UNIT) return __float_as_uint(__fmul_rn((float)__umulhi(h, m.m24), 0x1p-24f));
+    else if constexpr (MODE == B200V_GEN_DENORM) return h & 0x81FFFFFFu;
+    else return (h & 0x7F800000u) == 0x7F800000u ? h & ~0x00800000u : h;
+}
+
+template <int MODE> __device__ __forceinline__ uint32_t bf16_from_hash(uint32_t h, const ShiftMul& m)
+{
+    if constexpr (MODE == B200V_GEN_UNIT) return __float_as_uint(__fmul_rn((float)__umulhi(h, m.m8), 0x1p-8f)) >> 16;
+    else if constexpr (MODE == B200V_GEN_DENORM) return __umulhi(h, m.m16) & 0x81FFu;
+    else {
+        const uint32_t b = __umulhi(h, m.m16);
+        return (b & 0x7F80u) == 0x7F80u ? b & ~0x0080u : b;
+    }
+}
+
 // One thread produces 16 bytes (4 fp32 / 8 bf16) where dst is 16-byte aligned; the ragged
 // head and tail are written element-wise.
-template <bool BF16>
+template <bool BF16, int MODE>
 __global__ void __launch_bounds__(256)
-fill_kernel(void* __restrict__ dst, uint64_t start, size_t n, uint32_t key, int mode)
+fill_kernel(void* __restrict__ dst, uint64_t start, size_t n, uint32_t key, ShiftMul m)
 {
     constexpr size_t EPV = BF16 ? 8 : 4;
     constexpr size_t ESZ = BF16 ? 2 : 4;
@@ -170,17 +209,26 @@ fill_kernel(void* __restrict__ dst, uint64_t start, size_t n, uint32_t key, int 
     uint4* vdst = reinterpret_cast<uint4*>(reinterpret_cast<char*>(dst) + head * ESZ);
     for (size_t v = tid; v < nvec; v += stride) {
         const uint64_t i0 = start + head + v * EPV;
+        const uint32_t lo0 = (uint32_t)i0;
+        uint32_t w[EPV];
+        if (lo0 <= 0xFFFFFFFFu - (uint32_t)EPV) {
+            // all EPV indices share the high half: one hoisted term, 32-bit index arithmetic
+            const uint32_t kh = key ^ ((uint32_t)(i0 >> 32) * 0x9E3779B9u);
+#pragma unroll
+            for (int k = 0; k < (int)EPV; ++k) {
+                const uint32_t h = mix32_fma((lo0 + (uint32_t)k) ^ kh, m);
+                w[k] = BF16 ? bf16_from_hash<MODE>(h, m) : f32_from_hash<MODE>(h, m);
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < (int)EPV; ++k)
+                w[k] = BF16 ? gen_bf16_bits(key, i0 + k, MODE) : gen_f32_bits(key, i0 + k, MODE);
+        }
         uint4 o;
         if constexpr (!BF16) {
-            o.x = gen_f32_bits(key, i0 + 0, mode);
-            o.y = gen_f32_bits(key, i0 + 1, mode);
-            o.z = gen_f32_bits(key, i0 + 2, mode);
-            o.w = gen_f32_bits(key, i0 + 3, mode);
+            o = make_uint4(w[0], w[1], w[2], w[3]);
         } else {
-            o.x = gen_bf16_bits(key, i0 + 0, mode) | (gen_bf16_bits(key, i0 + 1, mode) << 16);
-            o.y = gen_bf16_bits(key, i0 + 2, mode) | (gen_bf16_bits(key, i0 + 3, mode) << 16);
-            o.z = gen_bf16_bits(key, i0 + 4, mode) | (gen_bf16_bits(key, i0 + 5, mode) << 16);
-            o.w = gen_bf16_bits(key, i0 + 6, mode) | (gen_bf16_bits(key, i0 + 7, mode) << 16);
+            o = make_uint4(w[0] | (w[1] << 16), w[2] | (w[3] << 16), w[4] | (w[5] << 16), w[6] | (w[7] << 16));
         }
         vdst[v] = o;
     }
@@ -189,8 +237,8 @@ fill_kernel(void* __restrict__ dst, uint64_t start, size_t n, uint32_t key, int 
     const size_t ragged = head + (n - tail0);
     for (size_t r = tid; r < ragged; r += stride) {
         const size_t j = r < head ? r : tail0 + (r - head);
-        if constexpr (!BF16) reinterpret_cast<uint32_t*>(dst)[j] = gen_f32_bits(key, start + j, mode);
-        else reinterpret_cast<uint16_t*>(dst)[j] = (uint16_t)gen_bf16_bits(key, start + j, mode);
+        if constexpr (!BF16) reinterpret_cast<uint32_t*>(dst)[j] = gen_f32_bits(key, start + j, MODE);
+        else reinterpret_cast<uint16_t*>(dst)[j] = (uint16_t)gen_bf16_bits(key, start + j, MODE);
     }
 }
 
@@ -320,10 +368,24 @@ int b200v_fill(int dtype, void* d_dst, uint64_t start, size_t n, uint32_t seed, 
     size_t grid = (n / epv + 255) / 256 + 1;
     const size_t cap = (size_t)sms * 16;
     if (grid > cap) grid = cap;
-    if (dtype == B200V_BF16)
-        fill_kernel<true><<<(unsigned)grid, 256, 0, as_stream(stream)>>>(d_dst, start, n, key, mode);
-    else
-        fill_kernel<false><<<(unsigned)grid, 256, 0, as_stream(stream)>>>(d_dst, start, n, key, mode);
+    const ShiftMul m = {1u << 16, 1u << 17, 1u << 24, 1u << 8};
+    cudaStream_t st = as_stream(stream);
+    const unsigned g = (unsigned)grid;
+    const bool bf = dtype == B200V_BF16;
+    switch (mode) {
+    case B200V_GEN_UNIT:
+        if (bf) fill_kernel<true, B200V_GEN_UNIT><<<g, 256, 0, st>>>(d_dst, start, n, key, m);
+        else fill_kernel<false, B200V_GEN_UNIT><<<g, 256, 0, st>>>(d_dst, start, n, key, m);
+        break;
+    case B200V_GEN_BITS:
+        if (bf) fill_kernel<true, B200V_GEN_BITS><<<g, 256, 0, st>>>(d_dst, start, n, key, m);
+        else fill_kernel<false, B200V_GEN_BITS><<<g, 256, 0, st>>>(d_dst, start, n, key, m);
+        break;
+    default:
+        if (bf) fill_kernel<true, B200V_GEN_DENORM><<<g, 256, 0, st>>>(d_dst, start, n, key, m);
+        else fill_kernel<false, B200V_GEN_DENORM><<<g, 256, 0, st>>>(d_dst, start, n, key, m);
+        break;
+    }
     B200V_CUDA(cudaGetLastError());
     return B200V_OK;
 }
