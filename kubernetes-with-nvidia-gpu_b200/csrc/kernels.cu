@@ -154,41 +154,26 @@ __device__ __forceinline__ uint32_t gen_bf16_bits(uint32_t key, uint64_t index, 
     return b;
 }
 
-// The vector body of the fill is integer-ALU bound if written naively (ncu: ALU pipe 95 %, DRAM 48 %).
-// Its fast path therefore (a) takes the generator mode as a template parameter, (b) hoists the
-// high-half term of the hash out of the per-element work (a vector that straddles a 2^32 index
-// boundary takes the plain path), and (c) does every `x >> s` as a multiply-high by 2^(32-s) so the
-// shifts run on the FMA pipe (IMAD.HI) beside the two hash multiplies and leave the ALU pipe the
-// XORs.  The multipliers arrive as kernel arguments so that ptxas cannot turn them back into shifts.
+// The fill is integer-ALU bound (ncu: ALU pipe 95 %, DRAM 48 % for the first version).  The vector
+// body therefore takes the generator mode as a template parameter and hoists the high-half term of
+// the hash out of the per-element work (32-bit index arithmetic; a vector that straddles a 2^32 index
+// boundary takes the plain path): 4.2 -> 5.9 TB/s for fp32, 3.6 -> 4.3 TB/s for bf16.  Doing the
+// shifts as multiply-high on the FMA pipe was tried and is slower (IMAD.HI is half rate).
 // Same integer function as mix32/hash32 above, bit for bit (tests/test_gpu_parity.py: fill vs oracle).
 
-struct ShiftMul {
-    uint32_t m16, m17, m24, m8;   // 2^16, 2^17 (>> 15), 2^24 (>> 8), 2^8 (>> 24)
-};
-
-__device__ __forceinline__ uint32_t mix32_fma(uint32_t x, const ShiftMul& m)
+template <int MODE> __device__ __forceinline__ uint32_t f32_from_hash(uint32_t h)
 {
-    x ^= __umulhi(x, m.m16);
-    x *= 0x7FEB352Du;
-    x ^= __umulhi(x, m.m17);
-    x *= 0x846CA68Bu;
-    x ^= __umulhi(x, m.m16);
-    return x;
-}
-
-template <int MODE> __device__ __forceinline__ uint32_t f32_from_hash(uint32_t h, const ShiftMul& m)
-{
-    if constexpr (MODE == B200V_GEN_UNIT) return __float_as_uint(__fmul_rn((float)__umulhi(h, m.m24), 0x1p-24f));
+    if constexpr (MODE == B200V_GEN_UNIT) return __float_as_uint(__fmul_rn((float)(h >> 8), 0x1p-24f));
     else if constexpr (MODE == B200V_GEN_DENORM) return h & 0x81FFFFFFu;
     else return (h & 0x7F800000u) == 0x7F800000u ? h & ~0x00800000u : h;
 }
 
-template <int MODE> __device__ __forceinline__ uint32_t bf16_from_hash(uint32_t h, const ShiftMul& m)
+template <int MODE> __device__ __forceinline__ uint32_t bf16_from_hash(uint32_t h)
 {
-    if constexpr (MODE == B200V_GEN_UNIT) return __float_as_uint(__fmul_rn((float)__umulhi(h, m.m8), 0x1p-8f)) >> 16;
-    else if constexpr (MODE == B200V_GEN_DENORM) return __umulhi(h, m.m16) & 0x81FFu;
+    if constexpr (MODE == B200V_GEN_UNIT) return __float_as_uint(__fmul_rn((float)(h >> 24), 0x1p-8f)) >> 16;
+    else if constexpr (MODE == B200V_GEN_DENORM) return (h >> 16) & 0x81FFu;
     else {
-        const uint32_t b = __umulhi(h, m.m16);
+        const uint32_t b = h >> 16;
         return (b & 0x7F80u) == 0x7F80u ? b & ~0x0080u : b;
     }
 }
@@ -197,7 +182,7 @@ template <int MODE> __device__ __forceinline__ uint32_t bf16_from_hash(uint32_t 
 // head and tail are written element-wise.
 template <bool BF16, int MODE>
 __global__ void __launch_bounds__(256)
-fill_kernel(void* __restrict__ dst, uint64_t start, size_t n, uint32_t key, ShiftMul m)
+fill_kernel(void* __restrict__ dst, uint64_t start, size_t n, uint32_t key)
 {
     constexpr size_t EPV = BF16 ? 8 : 4;
     constexpr size_t ESZ = BF16 ? 2 : 4;
@@ -216,8 +201,8 @@ fill_kernel(void* __restrict__ dst, uint64_t start, size_t n, uint32_t key, Shif
             const uint32_t kh = key ^ ((uint32_t)(i0 >> 32) * 0x9E3779B9u);
 #pragma unroll
             for (int k = 0; k < (int)EPV; ++k) {
-                const uint32_t h = mix32_fma((lo0 + (uint32_t)k) ^ kh, m);
-                w[k] = BF16 ? bf16_from_hash<MODE>(h, m) : f32_from_hash<MODE>(h, m);
+                const uint32_t h = mix32((lo0 + (uint32_t)k) ^ kh);
+                w[k] = BF16 ? bf16_from_hash<MODE>(h) : f32_from_hash<MODE>(h);
             }
         } else {
 #pragma unroll
@@ -368,22 +353,21 @@ int b200v_fill(int dtype, void* d_dst, uint64_t start, size_t n, uint32_t seed, 
     size_t grid = (n / epv + 255) / 256 + 1;
     const size_t cap = (size_t)sms * 16;
     if (grid > cap) grid = cap;
-    const ShiftMul m = {1u << 16, 1u << 17, 1u << 24, 1u << 8};
     cudaStream_t st = as_stream(stream);
     const unsigned g = (unsigned)grid;
     const bool bf = dtype == B200V_BF16;
     switch (mode) {
     case B200V_GEN_UNIT:
-        if (bf) fill_kernel<true, B200V_GEN_UNIT><<<g, 256, 0, st>>>(d_dst, start, n, key, m);
-        else fill_kernel<false, B200V_GEN_UNIT><<<g, 256, 0, st>>>(d_dst, start, n, key, m);
+        if (bf) fill_kernel<true, B200V_GEN_UNIT><<<g, 256, 0, st>>>(d_dst, start, n, key);
+        else fill_kernel<false, B200V_GEN_UNIT><<<g, 256, 0, st>>>(d_dst, start, n, key);
         break;
     case B200V_GEN_BITS:
-        if (bf) fill_kernel<true, B200V_GEN_BITS><<<g, 256, 0, st>>>(d_dst, start, n, key, m);
-        else fill_kernel<false, B200V_GEN_BITS><<<g, 256, 0, st>>>(d_dst, start, n, key, m);
+        if (bf) fill_kernel<true, B200V_GEN_BITS><<<g, 256, 0, st>>>(d_dst, start, n, key);
+        else fill_kernel<false, B200V_GEN_BITS><<<g, 256, 0, st>>>(d_dst, start, n, key);
         break;
     default:
-        if (bf) fill_kernel<true, B200V_GEN_DENORM><<<g, 256, 0, st>>>(d_dst, start, n, key, m);
-        else fill_kernel<false, B200V_GEN_DENORM><<<g, 256, 0, st>>>(d_dst, start, n, key, m);
+        if (bf) fill_kernel<true, B200V_GEN_DENORM><<<g, 256, 0, st>>>(d_dst, start, n, key);
+        else fill_kernel<false, B200V_GEN_DENORM><<<g, 256, 0, st>>>(d_dst, start, n, key);
         break;
     }
     B200V_CUDA(cudaGetLastError());

@@ -8,6 +8,8 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 pkg = importlib.import_module("kubernetes-with-nvidia-gpu_b200")
+if os.environ.get("B200V_LIB"):
+    pkg.LIB_PATH = os.environ["B200V_LIB"]
 L = pkg.lib()
 pkg.check(L.b200v_set_device(0))
 vp = C.c_void_p
