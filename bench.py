@@ -15,10 +15,23 @@ only for the barrier and the max-over-ranks of the device-timed durations.
 One JSON line on stdout (rank 0).  `value` = whole-job GB/s of algorithmic bytes (12 B/element);
 `e2e` = the same metric through b200v_vector_add_host with pinned HOST buffers (H2D + kernel +
 D2H inside the timed region); `roofline` = the add kernel against the measured HBM copy peak;
-`cpu_baseline` = the oracle's OpenMP loop on this box's host cores (a reported baseline).
-The oracle is only ever executed inside the cpu_baseline / --impl reference legs; at N = 1 that leg
-also yields the parity check of the whole timed output (its checksum must equal the device's).
-`--impl reference` times that CPU loop as the reference arm: the reference repo itself has no
+`cpu_baseline` = the oracle's OpenMP loop on this box's host cores (a reported baseline, N = 1).
+Further keys, all measured in the same run:
+  `triad`               the north-star kernel at the same size, separately timed;
+  `sustained`           >= 3 s of back-to-back add (and triad) launches under one event pair, with the
+                        NVML clock/power window over exactly that stretch (the loaded operating point);
+  `triad_sharded_2p32`  BASELINE.json configs[3]: 2^32 fp32 elements in total, contiguous shards over
+                        the ranks (strong scaling), device-timed, max over ranks, every shard's checksum
+                        compared with the oracle's;
+  `parity`              at every N: each rank's whole 2^28-element output against the oracle's loop over
+                        the same global indices (checksum), AND over ranks; the run fails if false;
+  `native_node`, `p2p`  rank 0, after every rank has freed its buffers: the pod entrypoint's own
+                        per-GPU shard launcher (`gpu-validate --mode node`, fork/exec + pipe barrier) on
+                        the same 2^32-element triad, and the all-pairs NVLink check (`--mode p2p`,
+                        BASELINE.json configs[4]) — the product binaries, run as subprocesses.
+The oracle is only ever executed as the checker (parity legs) or as the timed CPU baseline
+(`cpu_baseline`, `--impl reference`), never on the GPU arm's product path.
+`--impl reference` times the CPU loop as the reference arm: the reference repo itself has no
 compute code for this path (its Step 9 pod runs `nvidia-smi`), so the CPU restatement in oracle/
 is the reference implementation.
 """
@@ -29,6 +42,7 @@ import json
 import os
 import subprocess
 import sys
+import tempfile
 import threading
 import time
 
@@ -40,9 +54,18 @@ METRIC = "vectorAdd/triad HBM GB/s per GPU & node at 1/2/4/8 B200, % of ~8 TB/s 
 LOG2_N = 28
 N_ELEMS = 1 << LOG2_N
 BYTES_PER_STEP = 12 * N_ELEMS          # 12 B per fp32 element for add/triad
+SHARDED_LOG2 = 32                      # configs[3]: 2^32 fp32 elements in total
 NOMINAL_GBS = 8000.0
+NVLINK_GBS = 900.0
 FALLBACK_GBS = 6650.0                  # B200_PROFILING.md fallback when MEASURED_PEAKS.json is absent
 SEED = 20261106
+M64 = (1 << 64) - 1
+
+
+def host_cores():
+    return len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+
+
 def _cpu_sample_log2():
     """Elements per CPU step in the reference arm / cpu_baseline: the full 2^28 workload (3 GiB of
     arrays, larger than any host L3, like the GPU's) when host RAM allows, else 2^26."""
@@ -54,6 +77,18 @@ def _cpu_sample_log2():
 
 
 CPU_SAMPLE_LOG2 = _cpu_sample_log2()
+
+
+def workload_config(world):
+    """The `config` object of BOTH arms: it names the workload (BASELINE.json configs[1]) and nothing
+    that differs between the GPU arm and the CPU reference arm."""
+    return {
+        "workload": f"vectorAdd fp32 C=A+B, N=2^{LOG2_N} elements per GPU (BASELINE.json configs[1]), one pass over the arrays per step",
+        "elements_per_gpu": N_ELEMS, "bytes_per_step_per_gpu": BYTES_PER_STEP, "bytes_per_element": 12,
+        "parallelism": f"shard{world} (one process per GPU, no collective on the data path)",
+        "l2": f"the three arrays are {3 * 4 * N_ELEMS >> 20} MiB per GPU, far larger than the 126 MB L2 (and any host L3): no flush between steps",
+        "inputs": f"index-hash generator, UNIT mode (24-bit k * 2^-24), seed {SEED}, streams 0/1, resident before the timed region",
+    }
 
 
 def measured_peak():
@@ -75,7 +110,8 @@ def ncu_traffic_per_launch():
 
 # ------------------------------------------------------------------------------------------------
 class ClockSampler(threading.Thread):
-    """Samples SM clock and throttle reasons of one GPU through NVML while the timed region runs."""
+    """Samples SM clock, power and throttle reasons of one GPU through NVML while the bench runs;
+    `summary(a, b)` reports the samples between two named marks."""
 
     REASONS = {0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown",
                0x40: "hw_thermal_slowdown", 0x80: "hw_power_brake"}
@@ -124,28 +160,36 @@ class ClockSampler(threading.Thread):
     def mark(self, name):
         self.marks[name] = time.perf_counter()
 
-    def summary(self):
-        if not self.ok:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "note": "NVML unavailable: " + getattr(self, "err", "")}
-        t0, t1 = self.marks.get("timed_start", 0), self.marks.get("timed_end", float("inf"))
-        inside = [s for s in self.samples if t0 <= s[0] <= t1]
-        window = "timed region"
-        if len(inside) < 3:   # very short timed region: widen to warm-up .. end of the device-timed legs
-            inside = [s for s in self.samples if self.marks.get("load_start", 0) <= s[0] <= self.marks.get("load_end", t1)]
-            window = "warm-up + timed + triad legs (timed region shorter than 3 samples)"
-        if not inside:
-            inside = self.samples
+    def _window(self, a, b):
+        t0, t1 = self.marks.get(a, 0), self.marks.get(b, float("inf"))
+        return [s for s in self.samples if t0 <= s[0] <= t1]
+
+    def _describe(self, inside, window):
         mhz = sorted(s[1] for s in inside)
         mask = 0
         for s in inside:
             mask |= s[2]
         pw = [s[3] for s in inside if s[3] is not None]
-        return {"sm_mhz": mhz[len(mhz) // 2] if mhz else None, "sm_max_mhz": self.sm_max,
+        return {"sm_mhz": mhz[len(mhz) // 2] if mhz else None, "sm_mhz_min": mhz[0] if mhz else None, "sm_max_mhz": self.sm_max,
                 "reasons": [n for b, n in self.REASONS.items() if mask & b],
-                "power_w_max": max(pw) if pw else None, "samples": len(inside), "window": window}
+                "power_w_max": max(pw) if pw else None, "power_w_median": sorted(pw)[len(pw) // 2] if pw else None,
+                "samples": len(inside), "window": window}
+
+    def summary(self, a="timed_start", b="timed_end", widen=("load_start", "load_end")):
+        if not self.ok:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "note": "NVML unavailable: " + getattr(self, "err", "")}
+        inside, window = self._window(a, b), f"{a} .. {b}"
+        if len(inside) < 3 and widen:   # very short timed region: widen to warm-up .. end of the device-timed legs
+            inside = self._window(*widen)
+            window = f"{widen[0]} .. {widen[1]} (the {a} .. {b} region is shorter than 3 samples)"
+        if not inside:
+            inside, window = self.samples, "whole run"
+        return self._describe(inside, window)
 
 
 # ------------------------------------------------------------------------------------------------
+# CPU side: the oracle as the timed baseline and as the checker
+
 def cpu_step_runner(log2n):
     """Returns (run_one_step, cores, n): the oracle's OpenMP vectorAdd on host memory."""
     import numpy as np
@@ -158,7 +202,7 @@ def cpu_step_runner(log2n):
     pa, pb, pc = (x.ctypes.data_as(C.c_void_p) for x in (a, b, c))
 
     # every host core this process may run on; explicit, because torchrun exports OMP_NUM_THREADS=1
-    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    cores = host_cores()
 
     def step():
         L.oracle_add_f32(pc, pa, pb, n, cores)
@@ -191,6 +235,26 @@ def cpu_baseline(budget_s=10.0):
     return out
 
 
+def oracle_shard_checksum(op, start, count, word_offset, threads, s=3.0, chunk=1 << 24):
+    """The oracle as the checker: checksum of op(gen(stream 0), gen(stream 1), s) over global indices
+    [start, start+count), word indices counted from word_offset, computed in chunks so host RAM never
+    holds the arrays (the same walk as tests/test_gpu_parity.py::oracle_checksum_chunked)."""
+    import oracle_lib as O
+    tot = [0, 0]
+    for off in range(0, count, chunk):
+        m = min(chunk, count - off)
+        x = O.fill("f32", start + off, m, SEED, 0)
+        y = O.fill("f32", start + off, m, SEED, 1)
+        out = O.op(op, "f32", m, s=s, x=x, y=y, threads=threads)
+        c = O.checksum(out, word_offset + off, threads=threads)
+        tot = [(tot[0] + c[0]) & M64, (tot[1] + c[1]) & M64]
+    return tot[0], tot[1]
+
+
+def hex_pair(p):
+    return ["%016x" % p[0], "%016x" % p[1]]
+
+
 def run_reference(args, rank):
     """Reference arm: the CPU implementation of the path on this box's host cores."""
     if rank != 0:
@@ -204,18 +268,74 @@ def run_reference(args, rank):
     dt = time.perf_counter() - t0
     gbs = 12.0 * n * args.steps / dt * 1e-9
     sample = (f"each step = oracle_add_f32 (OpenMP, {cores} threads) over N=2^{CPU_SAMPLE_LOG2} fp32 elements resident in "
-              f"host RAM, {'the full' if CPU_SAMPLE_LOG2 == LOG2_N else 'a bounded sample of the'} 2^{LOG2_N} workload")
+              f"host RAM, {'the full' if CPU_SAMPLE_LOG2 == LOG2_N else 'a bounded sample of the'} 2^{LOG2_N}-element per-GPU workload")
     line = {
         "impl": "reference", "metric": METRIC, "value": round(gbs, 2), "unit": "GB/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(dt / args.steps * 1e3, 4),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"vectorAdd fp32 C=A+B, N=2^{LOG2_N} per GPU (BASELINE.json configs[1]); CPU arm runs a "
-                               f"2^{CPU_SAMPLE_LOG2}-element sample per step", "bytes_per_element": 12},
+        "config": workload_config(args.gpus),
         "cpu_baseline": {"value": round(gbs, 2), "unit": "GB/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": round(gbs, 2), "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+# rank 0: the product's own binaries as subprocesses (native shard launcher, NVLink check)
+
+def run_native(pkg, mode_args, json_name, timeout):
+    """Runs gpu-validate with --json; returns a dict: rc, verdict line, parsed json (or None), summary lines."""
+    with tempfile.TemporaryDirectory() as td:
+        js = os.path.join(td, json_name)
+        cmd = [pkg.LAUNCHER_PATH, *mode_args, "--json", js]
+        env = dict(os.environ, OMP_NUM_THREADS=str(host_cores()))     # torchrun exports OMP_NUM_THREADS=1
+        t0 = time.perf_counter()
+        try:
+            r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, env=env)
+            rc, out = r.returncode, r.stdout
+        except subprocess.TimeoutExpired:
+            rc, out = -1, f"timed out after {timeout} s"
+        wall = time.perf_counter() - t0
+        lines = out.strip().splitlines()
+        data = None
+        try:
+            with open(js) as f:
+                data = json.load(f)
+        except Exception:
+            pass
+        return {"rc": rc, "verdict": lines[-1] if lines else "", "json": data, "wall_s": round(wall, 1),
+                "summary_lines": [ln for ln in lines if ln.startswith(("[node]", "[p2p]", "reason:"))],
+                "cmd": "gpu-validate " + " ".join(mode_args)}
+
+
+def native_node_leg(pkg, world, iters):
+    r = run_native(pkg, ["--mode", "node", "--gpus", str(world), "--log2n", str(SHARDED_LOG2), "--iters", str(iters)], "node.json", 600)
+    d = r.pop("json")
+    out = dict(r, what="the pod entrypoint's per-GPU shard launcher (fork/exec one child per GPU, pipe start barrier, max over ranks), "
+                       f"triad over 2^{SHARDED_LOG2} fp32 elements in total (BASELINE.json configs[3]); every shard verified against the host loop's checksum")
+    if d:
+        out.update({"gpus": d["gpus"], "elements": d["elements"], "node_gbs": d["node_gbs"], "node_gbs_from": d.get("node_gbs_from"),
+                    "max_mean_ms": d["max_mean_ms"], "max_best_ms": d["max_best_ms"], "node_best_gbs": d.get("node_best_gbs"),
+                    "gbs_per_gpu": round(d["node_gbs"] / d["gpus"], 1),
+                    "frac_of_nominal_8000_per_gpu": round(d["node_gbs"] / d["gpus"] / NOMINAL_GBS, 4),
+                    "verified": bool(d["ok"]) and all(k["ok"] == 1 for k in d["ranks"]),
+                    "ranks": [{"rank": k["rank"], "ok": k["ok"], "elements": k["elements"], "mean_ms": k["mean_ms"], "best_ms": k["best_ms"]}
+                              for k in d["ranks"]]})
+    out["ok"] = out["rc"] == 0 and out["verdict"] == "Test PASSED" and bool(d) and out.get("verified", False)
+    return out
+
+
+def native_p2p_leg(pkg, world, p2p_bytes):
+    r = run_native(pkg, ["--mode", "p2p", "--gpus", str(world), "--p2p-bytes", str(p2p_bytes), "--iters", "12"], "p2p.json", 600)
+    d = r.pop("json")
+    out = dict(r, what="all ordered GPU pairs over NVLink (BASELINE.json configs[4]): cudaMemcpyPeer, a kernel loading from the peer, a kernel "
+                       "storing into the peer; then every GPU sending and receiving at once; every transfer verified by checksum on the destination")
+    if d:
+        out.update({"gpus": d["gpus"], "bytes_per_transfer": d["bytes"], "pairs": len(d["pairs"]), "verified": bool(d["ok"]),
+                    "nvlink_gbs_per_direction": d.get("nvlink_gbs_per_direction", NVLINK_GBS), "gbs": d.get("summary")})
+    out["ok"] = out["rc"] == 0 and out["verdict"] == "Test PASSED" and bool(d) and out.get("verified", False)
+    return out
 
 
 # ------------------------------------------------------------------------------------------------
@@ -225,15 +345,22 @@ def main():
     ap.add_argument("--steps", type=int, default=1000)
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="vectoradd", choices=["vectoradd", "triad-sharded"],
-                    help="vectoradd: configs[1], 2^28 fp32 per GPU (weak, the default and the graded line); "
-                         "triad-sharded: configs[3], 2^32 fp32 in total split over the ranks (strong)")
     ap.add_argument("--e2e-steps", type=int, default=8)
-    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--sustained-seconds", type=float, default=3.0, help="length of each sustained leg (add, triad)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (N = 1) and every oracle parity leg")
+    ap.add_argument("--no-sharded", action="store_true", help="skip the 2^32-element sharded triad leg")
+    ap.add_argument("--no-native", action="store_true", help="skip the gpu-validate subprocess legs (native_node, p2p)")
+    ap.add_argument("--p2p-bytes", type=int, default=1 << 30)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
 
+    world_env = int(os.environ.get("WORLD_SIZE", "1"))
+    # torchrun exports OMP_NUM_THREADS=1; the oracle legs (the checker) get this rank's share of the host cores
+    threads = max(1, host_cores() // world_env)
+    os.environ["OMP_NUM_THREADS"] = str(threads)
+
     if args.impl == "reference":
+        os.environ["OMP_NUM_THREADS"] = str(host_cores())
         run_reference(args, int(os.environ.get("RANK", "0")))
         return 0
 
@@ -241,31 +368,14 @@ def main():
     pkg = importlib.import_module("kubernetes-with-nvidia-gpu_b200")
     ranks_mod = importlib.import_module("kubernetes-with-nvidia-gpu_b200.ranks")
     L = pkg.lib()          # raises if libb200v.so is missing: no fallback
-    R = ranks_mod.Ranks(backend="nccl" if int(os.environ.get("WORLD_SIZE", "1")) > 1 else None,
+    R = ranks_mod.Ranks(backend="nccl" if world_env > 1 else None,
                         device_sync=lambda: pkg.check(L.b200v_device_sync()))
     rank, local_rank, world = R.rank, R.local_rank, R.world
     pkg.check(L.b200v_set_device(local_rank))
     pkg.check(L.b200v_require_sm100(local_rank))
     info = pkg.device_info(local_rank)
 
-    sharded = args.workload == "triad-sharded"
-    if sharded:
-        total = 1 << 32
-        start, n_local = pkg.shard_range(total, rank, world)
-        main_op, main_name = pkg.OP_TRIAD, "triad"
-    else:
-        n_local = N_ELEMS
-        start = rank * N_ELEMS          # rank r owns [r*N, (r+1)*N) of the job's global index space
-        total = world * N_ELEMS
-        main_op, main_name = pkg.OP_ADD, "add"
-    bytes_local = 12 * n_local
-    bytes_job = 12 * total
-
     vp = C.c_void_p
-    nbytes = 4 * n_local
-    dA, dB, dC = (pkg.DeviceBuffer(nbytes) for _ in range(3))
-    pkg.check(L.b200v_fill(pkg.F32, vp(dA.ptr), start, n_local, SEED, 0, pkg.GEN_UNIT, None))
-    pkg.check(L.b200v_fill(pkg.F32, vp(dB.ptr), start, n_local, SEED, 1, pkg.GEN_UNIT, None))
     stream = vp(None)
     pkg.check(L.b200v_stream_create(C.byref(stream)))
     ev0, ev1 = vp(None), vp(None)
@@ -276,6 +386,7 @@ def main():
     sampler.start()
 
     def timed(fn, steps):
+        """K launches between two events on the launching stream, barrier + sync on both sides; local ms."""
         R.barrier()
         pkg.check(L.b200v_event_record(ev0, stream))
         for _ in range(steps):
@@ -287,37 +398,109 @@ def main():
         pkg.check(L.b200v_event_elapsed_ms(ev0, ev1, C.byref(ms)))
         return ms.value
 
+    def timed_for(fn, seconds, est_ms):
+        """At least `seconds` of back-to-back launches under ONE event pair; returns (local ms, launches)."""
+        launches = max(int(seconds * 1e3 / est_ms) + 1, 3)
+        return timed(fn, launches), launches
+
+    # ---- configs[1]: vectorAdd, 2^28 fp32 per GPU; rank r owns [r*N, (r+1)*N) of the job's index space ----
+    n_local = N_ELEMS
+    start = rank * N_ELEMS
+    total = world * N_ELEMS
+    bytes_local = 12 * n_local
+    bytes_job = 12 * total
+    nbytes = 4 * n_local
+    dA, dB, dC = (pkg.DeviceBuffer(nbytes) for _ in range(3))
+    # inputs are filled on the launching stream: the warm-up cannot start before they are complete
+    pkg.check(L.b200v_fill(pkg.F32, vp(dA.ptr), start, n_local, SEED, 0, pkg.GEN_UNIT, stream))
+    pkg.check(L.b200v_fill(pkg.F32, vp(dB.ptr), start, n_local, SEED, 1, pkg.GEN_UNIT, stream))
+    pkg.check(L.b200v_stream_sync(stream))
+
     add = lambda: pkg.check(L.b200v_add_f32(vp(dC.ptr), vp(dA.ptr), vp(dB.ptr), n_local, stream))
     triad = lambda: pkg.check(L.b200v_triad_f32(vp(dC.ptr), 3.0, vp(dA.ptr), vp(dB.ptr), n_local, stream))
-    main_fn, other_fn = (triad, add) if sharded else (add, triad)
 
     # ---- device-resident leg (value): W warm-up steps, then exactly K timed steps ----
     sampler.mark("load_start")
     for _ in range(args.warmup):
-        main_fn()
+        add()
     sampler.mark("timed_start")
-    ms_local = timed(main_fn, args.steps)
+    ms_local = timed(add, args.steps)
     sampler.mark("timed_end")
     ms_total = R.max(ms_local)
     ms_per_step = ms_total / args.steps
     value = bytes_job / ms_per_step * 1e-6
 
-    # checksum of what was just timed (whole output of every rank, summed); at N = 1 the cpu_baseline leg
-    # below recomputes the same vector with the oracle and the two must agree
+    # checksum of what was just timed: this rank's whole output, word indices counted from its first global
+    # index, so the ranks' pairs add up to the checksum of the job's whole vector
     local_checksum = pkg.checksum(vp(dC.ptr), nbytes, start)
     job_checksum = R.sum_checksums(local_checksum)
 
     # the other 12 B/element kernel as a second, separately timed line (triad is the north-star kernel)
     for _ in range(args.warmup):
-        other_fn()
-    other_steps = max(min(args.steps, 200), 3)
-    other_ms = R.max(timed(other_fn, other_steps)) / other_steps
+        triad()
+    triad_steps = max(min(args.steps, 200), 3)
+    triad_ms = R.max(timed(triad, triad_steps)) / triad_steps
     sampler.mark("load_end")
-    other_gbs = bytes_job / other_ms * 1e-6
+    triad_gbs = bytes_job / triad_ms * 1e-6
 
-    # ---- end-to-end leg: host buffers through the public call, copies inside the timed region ----
+    # ---- sustained legs: >= S seconds of back-to-back launches, one event pair, NVML window over exactly that ----
+    sustained = {}
+    if args.sustained_seconds > 0:
+        for name, fn in (("add", add), ("triad", triad)):
+            sampler.mark(f"sustained_{name}_start")
+            ms_s, launches = timed_for(fn, args.sustained_seconds, ms_local / args.steps)
+            sampler.mark(f"sustained_{name}_end")
+            ms_s_max = R.max(ms_s)
+            gbs = bytes_job * launches / ms_s_max * 1e-6
+            sustained[name] = {"gbs": round(gbs, 1), "gbs_per_gpu": round(gbs / world, 1), "launches_per_gpu": launches,
+                               "seconds": round(ms_s_max * 1e-3, 3), "ms_per_launch": round(ms_s_max / launches, 5),
+                               "frac_of_nominal_8000_per_gpu": round(gbs / world / NOMINAL_GBS, 4),
+                               "clocks": sampler.summary(f"sustained_{name}_start", f"sustained_{name}_end", widen=None)}
+        sustained["gbs"] = sustained["add"]["gbs"]
+        sustained["vs_value"] = round(sustained["add"]["gbs"] / value, 4)
+        sustained["what"] = (f"back-to-back b200v_add_f32 / b200v_triad_f32 launches at N=2^{LOG2_N} per GPU for >= {args.sustained_seconds:g} s each, "
+                             "one event pair around all of them, max over ranks; clocks = rank 0's GPU over exactly that stretch")
+
     for b in (dA, dB, dC):
         b.free()
+
+    # ---- configs[3]: triad over 2^32 fp32 elements in total, contiguous shards (strong scaling) ----
+    sharded = None
+    sharded_ok = True
+    if not args.no_sharded:
+        tot32 = 1 << SHARDED_LOG2
+        s_begin, s_count = pkg.shard_range(tot32, rank, world)
+        sb = 4 * s_count
+        sOut, sX, sY = (pkg.DeviceBuffer(sb) for _ in range(3))     # out = fma(3, x, y)
+        pkg.check(L.b200v_fill(pkg.F32, vp(sX.ptr), s_begin, s_count, SEED, 0, pkg.GEN_UNIT, stream))
+        pkg.check(L.b200v_fill(pkg.F32, vp(sY.ptr), s_begin, s_count, SEED, 1, pkg.GEN_UNIT, stream))
+        pkg.check(L.b200v_stream_sync(stream))
+        striad = lambda: pkg.check(L.b200v_triad_f32(vp(sOut.ptr), 3.0, vp(sX.ptr), vp(sY.ptr), s_count, stream))
+        for _ in range(args.warmup):
+            striad()
+        pkg.check(L.b200v_memset(vp(sOut.ptr), 0x5A, sb, stream))   # the timed launches, not the warm-up, must produce the result
+        s_steps = max(min(args.steps, 50), 3)
+        s_ms_local = timed(striad, s_steps)
+        s_ms = R.max(s_ms_local) / s_steps
+        s_local_ck = pkg.checksum(vp(sOut.ptr), sb, s_begin)
+        s_job_ck = R.sum_checksums(s_local_ck)
+        for b in (sOut, sX, sY):
+            b.free()
+        sharded = {"elements_total": tot32, "elements_this_rank": s_count, "scaling": "strong", "steps": s_steps,
+                   "ms_per_step": round(s_ms, 5), "node_gbs": round(12 * tot32 / s_ms * 1e-6, 1),
+                   "gbs_per_gpu": round(12 * tot32 / s_ms * 1e-6 / world, 1),
+                   "frac_of_nominal_8000_per_gpu": round(12 * tot32 / s_ms * 1e-6 / world / NOMINAL_GBS, 4),
+                   "job_checksum": hex_pair(s_job_ck), "matches_oracle": None,
+                   "what": f"b200v_triad_f32 over this rank's b200v_shard_range share of 2^{SHARDED_LOG2} fp32 elements (BASELINE.json configs[3]); "
+                           "device-timed, max over ranks; the output is scrubbed after the warm-up and every rank's checksum is compared with the oracle's"}
+        if not args.no_cpu:      # the oracle, as the checker, over this rank's shard
+            t0 = time.perf_counter()
+            want = oracle_shard_checksum("triad", s_begin, s_count, s_begin, threads)
+            sharded_ok = R.all_ok(want == s_local_ck)
+            sharded["matches_oracle"] = sharded_ok
+            sharded["oracle_seconds"] = round(time.perf_counter() - t0, 1)
+
+    # ---- end-to-end leg: host buffers through the public call, copies inside the timed region ----
     n_e2e = N_ELEMS
     e2e_bytes = 4 * n_e2e
     hA, hB, hC = (pkg.PinnedBuffer(e2e_bytes) for _ in range(3))
@@ -340,78 +523,90 @@ def main():
     R.barrier()
     e2e_ms = R.max(e2e_ms_local) / args.e2e_steps
     e2e_value = world * 12 * n_e2e / e2e_ms * 1e-6
+
     # the host result must be the vector the device-resident leg produced (same inputs, same kernel, plus the
-    # H2D/D2H pipeline): compare checksums; at N = 1 and the vectoradd workload that is the timed output itself
+    # H2D/D2H pipeline): compare checksums
     def host_checksum(words, word_offset):
         idx = (np.arange(words.size, dtype=np.uint64) + np.uint64(word_offset)) & np.uint64(0xFFFFFFFF) | np.uint64(1)
         w64 = words.astype(np.uint64)
         return int(w64.sum(dtype=np.uint64)), int((w64 * idx).sum(dtype=np.uint64))
-    if sharded:
-        e2e_ok = True          # different op and shard: covered by tests/test_gpu_parity.py::test_vector_add_host_buffers
-        e2e_note = "not compared in the sharded workload"
-    else:
-        e2e_ok = host_checksum(vc, start) == local_checksum
-        e2e_note = "host result checksum == device-resident result checksum"
-    e2e_ok = R.all_ok(e2e_ok)
+    e2e_ok = R.all_ok(host_checksum(vc, start) == local_checksum)
     pkg.check(L.b200v_vector_add_host_release())
     del va, vb, vc
     for h in (hA, hB, hC):
         h.free()
 
+    # ---- parity of the timed output against the oracle, at every N ----
+    # N = 1: the cpu_baseline leg below recomputes the same vector (and is the timed CPU baseline as well).
+    # N > 1: every rank runs the oracle, as the checker, over ITS OWN global index range; AND over ranks.
+    parity_ok = None
+    parity_how = None
+    if not args.no_cpu and world > 1:
+        t0 = time.perf_counter()
+        want = oracle_shard_checksum("add", start, n_local, start, threads)
+        parity_ok = R.all_ok(want == local_checksum)
+        parity_how = (f"every rank: oracle loop over its own global indices [r*2^{LOG2_N}, (r+1)*2^{LOG2_N}) on {threads} host threads, "
+                      f"checksum == the device's ({time.perf_counter() - t0:.1f} s on rank 0); AND over ranks")
+
     sampler.stop_flag = True
     sampler.join(timeout=2)
     R.barrier()
+
+    # ---- rank 0 alone: the product's own launcher binaries; the other ranks wait on the host (no GPU work) ----
+    native_node = p2p = None
+    if rank == 0 and not args.no_native and os.path.exists(pkg.LAUNCHER_PATH):
+        native_node = native_node_leg(pkg, world, iters=20)
+        if world > 1:
+            p2p = native_p2p_leg(pkg, world, args.p2p_bytes)
+    R.host_barrier()
     if rank != 0:
         R.close()
         return 0
 
     peak, peak_src = measured_peak()
     achieved = bytes_local / (ms_local / args.steps) * 1e-6     # rank 0's kernel, GB/s
-    other_name = "add" if sharded else "triad"
+    cfg = workload_config(world)
     line = {
         "metric": METRIC, "value": round(value, 1), "unit": "GB/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": round(ms_per_step, 5), "higher_is_better": True,
-        "scaling": "strong" if sharded else "weak",
-        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {
-            "workload": ("triad fp32 a=fma(s,c,b), 2^32 elements in total sharded over the ranks (BASELINE.json configs[3])" if sharded else
-                         f"vectorAdd fp32 C=A+B, N=2^{LOG2_N} elements per GPU (BASELINE.json configs[1])") + ", one kernel launch per step",
-            "elements_per_gpu": n_local, "bytes_per_step_per_gpu": bytes_local, "bytes_per_element": 12,
-            "parallelism": f"shard{world} (one process per GPU, no collective on the data path)",
-            "l2": f"the three arrays are {3 * nbytes >> 20} MiB per GPU, far larger than the 126 MB L2: no flush between steps",
-            "gpu": info.name.decode(), "sm_count": info.sm_count,
-            "inputs": f"index-hash generator, UNIT mode (24-bit k * 2^-24), seed {SEED}, streams 0/1, filled on the device before the timed region",
-        },
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": cfg,
+        "device": {"gpu": info.name.decode(), "sm_count": info.sm_count, "host_cores": host_cores()},
         "roofline": {
             "bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
-            "frac": round(achieved / peak, 4), "traffic": None if sharded else ncu_traffic_per_launch(),
-            "peak_source": peak_src, "kernel": f"b200v::stream_kernel<{main_name}, f32, 256-bit> via b200v_{main_name}_f32",
+            "frac": round(achieved / peak, 4), "traffic": ncu_traffic_per_launch(),
+            "peak_source": peak_src, "kernel": "b200v::stream_kernel<add, f32, 256-bit> via b200v_add_f32",
             "algorithmic_bytes_per_launch": bytes_local,
             "frac_of_nominal_8000": round(achieved / NOMINAL_GBS, 4),
         },
-        other_name: {"node_gbs": round(other_gbs, 1), "gbs_per_gpu": round(other_gbs / world, 1), "ms_per_step": round(other_ms, 5),
-                     "steps": other_steps, "frac_of_measured": round(other_gbs / world / peak, 4),
-                     "frac_of_nominal_8000": round(other_gbs / world / NOMINAL_GBS, 4)},
+        "triad": {"node_gbs": round(triad_gbs, 1), "gbs_per_gpu": round(triad_gbs / world, 1), "ms_per_step": round(triad_ms, 5),
+                  "steps": triad_steps, "frac_of_measured": round(triad_gbs / world / peak, 4),
+                  "frac_of_nominal_8000": round(triad_gbs / world / NOMINAL_GBS, 4)},
+        "sustained": sustained or None,
+        "triad_sharded_2p32": sharded,
         "e2e": {"value": round(e2e_value, 2), "unit": "GB/s", "h2d_bytes_per_step": 8 * n_e2e * world,
                 "d2h_bytes_per_step": 4 * n_e2e * world, "ms_per_step": round(e2e_ms, 3), "steps": args.e2e_steps,
                 "api": f"b200v_vector_add_host(hA, hB, hC, 2^{LOG2_N}) per rank with pinned host buffers; host wall clock around "
                        "the synchronous call, max over ranks; bound by PCIe (2 GiB in + 1 GiB out per step per GPU)"},
         "gpu_launches": args.steps * world, "gpu_launches_per_rank": args.steps,
-        "parity": {"job_checksum": ["%016x" % job_checksum[0], "%016x" % job_checksum[1]],
-                   "e2e_matches_device": e2e_ok, "e2e_check": e2e_note,
-                   "device_matches_cpu_baseline": None},
+        "parity": {"job_checksum": hex_pair(job_checksum),
+                   "e2e_matches_device": e2e_ok, "e2e_check": "host result checksum == device-resident result checksum, every rank",
+                   "device_matches_cpu_baseline": parity_ok, "how": parity_how},
+        "native_node": native_node, "p2p": p2p,
         "clocks": sampler.summary(),
     }
-    parity_ok = True
-    if not args.no_cpu and world == 1:      # reported on rank 0 at N=1 only
+    if not args.no_cpu and world == 1:      # the timed CPU baseline is reported on rank 0 at N = 1 only
         line["cpu_baseline"] = cpu_baseline()
         want = line["cpu_baseline"].get("output_checksum")
-        if want is not None and not sharded:   # whole 2^28 output, GPU vs the oracle's loop: bit-exact or the run fails
+        if want is not None:   # whole 2^28 output, GPU vs the oracle's loop: bit-exact or the run fails
             parity_ok = want == line["parity"]["job_checksum"]
             line["parity"]["device_matches_cpu_baseline"] = parity_ok
+            line["parity"]["how"] = "the cpu_baseline leg's output (oracle loop over the same 2^28 global indices): checksum == the device's"
     print(json.dumps(line), flush=True)
     R.close()
-    return 0 if (parity_ok and e2e_ok) else 1
+    ok = (parity_ok is not False) and e2e_ok and sharded_ok
+    ok = ok and (native_node is None or native_node["ok"]) and (p2p is None or p2p["ok"])
+    return 0 if ok else 1
 
 
 if __name__ == "__main__":

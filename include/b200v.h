@@ -146,11 +146,14 @@ B200V_API uint64_t b200v_op_bytes(int op, int dtype, size_t n);
 /* ---- vectorAdd with HOST buffers, the cuda-samples call shape ------------------------------
  * hC = hA + hB for n fp32 elements held in host memory: H2D, kernel, D2H, all inside the
  * call, chunked and pipelined over copy engines.  Pinned buffers (b200v_host_alloc) get
- * PCIe speed; pageable ones work but are staged by the driver.  Synchronous.                */
+ * PCIe speed; pageable ones work but are staged by the driver.  Synchronous on every path: when
+ * the call returns — with B200V_OK or with an error — no copy from hA/hB or into hC is still in
+ * flight, so the caller may free or reuse the host buffers at once.                          */
 B200V_API int b200v_vector_add_host(const float *hA, const float *hB, float *hC, size_t n);
 B200V_API int b200v_vector_add_host_release(void);   /* frees the per-device staging buffers */
-/* pipeline shape: elements per staged chunk and number of chunk slots (streams) in flight;
- * takes effect at the next b200v_vector_add_host call.  Defaults: 8 Mi elements, 3 slots.    */
+/* pipeline shape of the CURRENT device: elements per staged chunk and number of chunk slots
+ * (streams) in flight; takes effect at that device's next b200v_vector_add_host call.
+ * Defaults: 8 Mi elements, 3 slots.                                                          */
 B200V_API int b200v_vector_add_host_config(size_t chunk_elems, int slots);
 
 /* ---- checksum (verifies outputs too large to bring back) -----------------------------------
@@ -173,7 +176,11 @@ B200V_API int b200v_checksum(const void *d_buf, size_t nbytes, uint64_t word_off
  *  - at most B200V_CHECKSUM_STATIC_MAX_BYTES per call, else B200V_ERR_INVALID (split the buffer:
  *    pieces add up; or use b200v_checksum);
  *  - the first call on each device also looks up the array's device address: make it at start-up,
- *    with that device current, before any stream capture begins;
+ *    with that device current, before any stream capture begins, and from one host thread (the
+ *    look-up is not locked; it falls under this header's one-host-thread-per-device rule);
+ *  - the address is remembered for the life of the process: do not call cudaDeviceReset (or tear
+ *    down the primary context) between calls — the remembered address would point into a dead
+ *    context and the next call would fail or write through it;
  *  - all calls on a device share the array: calls that overlap on the GPU race, so keep them on
  *    one stream or order them with events.                                                      */
 #define B200V_CHECKSUM_STATIC_MAX_BYTES (1ull << 32)
@@ -210,8 +217,13 @@ B200V_API int b200v_shard_range(uint64_t n, int rank, int world, uint64_t *begin
 B200V_API int b200v_peer_enable(int device, int peer);      /* idempotent */
 /* cudaMemcpyPeerAsync on `stream` of the current device */
 B200V_API int b200v_peer_copy(void *dst, int dst_device, const void *src, int src_device, size_t bytes, void *stream);
-/* kernel on the CURRENT device pulling `bytes` from a peer's buffer with direct 256-bit loads */
+/* kernel on the CURRENT device (the destination) pulling `bytes` from a peer's buffer with direct
+ * 256-bit loads: read requests go out, data comes back */
 B200V_API int b200v_peer_pull(void *d_local_dst, const void *d_peer_src, size_t bytes, void *stream);
+/* kernel on the CURRENT device (the source) pushing `bytes` of its own buffer into a peer's with direct
+ * 256-bit stores: posted writes, nothing but acknowledgements on the return path, so it keeps its
+ * rate when every GPU sends and receives at once.  Peer access current -> peer must be enabled.   */
+B200V_API int b200v_peer_push(void *d_peer_dst, const void *d_local_src, size_t bytes, void *stream);
 
 #ifdef __cplusplus
 }

@@ -121,6 +121,7 @@ def _signatures():
         "b200v_peer_enable": (i32, [i32, i32]),
         "b200v_peer_copy": (i32, [vp, i32, vp, i32, sz, vp]),
         "b200v_peer_pull": (i32, [vp, vp, sz, vp]),
+        "b200v_peer_push": (i32, [vp, vp, sz, vp]),
     }
     return s
 

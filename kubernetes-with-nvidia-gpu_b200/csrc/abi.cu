@@ -378,12 +378,16 @@ int b200v_shard_range(uint64_t n, int rank, int world, uint64_t* begin, uint64_t
 namespace {
 
 constexpr int kMaxSlots = 8;
-// defaults from the round-1 sweep (profiles/): see b200v_vector_add_host_config
-int g_slots = 3;
-size_t g_chunk_elems = (size_t)8 << 20;  // 8 Mi fp32 = 32 MiB per array per slot
+// defaults from the round-1 sweep (profiles/r01_e2e_sweep.json): see b200v_vector_add_host_config
+constexpr int kDefaultSlots = 3;
+constexpr size_t kDefaultChunkElems = (size_t)8 << 20;  // 8 Mi fp32 = 32 MiB per array per slot
 
+// One pipeline per device ordinal; its shape (want_*) is set per device too, so a process driving
+// several GPUs can shape each one's pipeline on its own.
 struct HostPipe {
     bool ready = false;
+    int want_slots = kDefaultSlots;
+    size_t want_chunk_elems = kDefaultChunkElems;
     int slots = 0;
     size_t chunk_elems = 0;
     cudaStream_t stream[kMaxSlots] = {};
@@ -410,10 +414,10 @@ int pipe_release(HostPipe& p)
 
 int pipe_init(HostPipe& p)
 {
-    if (p.ready && p.slots == g_slots && p.chunk_elems == g_chunk_elems) return B200V_OK;
+    if (p.ready && p.slots == p.want_slots && p.chunk_elems == p.want_chunk_elems) return B200V_OK;
     if (p.ready) pipe_release(p);
-    p.slots = g_slots;
-    p.chunk_elems = g_chunk_elems;
+    p.slots = p.want_slots;
+    p.chunk_elems = p.want_chunk_elems;
     for (int i = 0; i < p.slots; ++i) {
         cudaError_t e = cudaStreamCreateWithFlags(&p.stream[i], cudaStreamNonBlocking);
         if (e == cudaSuccess) e = cudaMalloc((void**)&p.a[i], p.chunk_elems * sizeof(float));
@@ -428,6 +432,27 @@ int pipe_init(HostPipe& p)
     return B200V_OK;
 }
 
+int current_pipe(HostPipe** out)
+{
+    int dev = 0;
+    B200V_CUDA(cudaGetDevice(&dev));
+    B200V_REQUIRE(dev >= 0 && dev < 64, B200V_ERR_INVALID, "device index %d out of range", dev);
+    *out = &g_pipe[dev];
+    return B200V_OK;
+}
+
+// one chunk: H2D of both inputs, the add kernel, D2H of the result, all on the slot's stream
+int enqueue_chunk(HostPipe& p, int slot, const float* hA, const float* hB, float* hC, size_t m)
+{
+    cudaStream_t st = p.stream[slot];
+    // stream order makes the slot's previous D2H finish before its buffers are overwritten
+    B200V_CUDA(cudaMemcpyAsync(p.a[slot], hA, m * sizeof(float), cudaMemcpyHostToDevice, st));
+    B200V_CUDA(cudaMemcpyAsync(p.b[slot], hB, m * sizeof(float), cudaMemcpyHostToDevice, st));
+    if (int rc = b200v_add_f32(p.c[slot], p.a[slot], p.b[slot], m, st)) return rc;
+    B200V_CUDA(cudaMemcpyAsync(hC, p.c[slot], m * sizeof(float), cudaMemcpyDeviceToHost, st));
+    return B200V_OK;
+}
+
 }  // namespace
 
 int b200v_vector_add_host_config(size_t chunk_elems, int slots)
@@ -435,8 +460,10 @@ int b200v_vector_add_host_config(size_t chunk_elems, int slots)
     B200V_REQUIRE(slots >= 1 && slots <= kMaxSlots, B200V_ERR_INVALID, "slots %d not in [1, %d]", slots, kMaxSlots);
     B200V_REQUIRE(chunk_elems >= 1024 && chunk_elems <= ((size_t)1 << 30), B200V_ERR_INVALID,
                   "chunk_elems %zu not in [1024, 2^30]", chunk_elems);
-    g_slots = slots;
-    g_chunk_elems = chunk_elems;
+    HostPipe* p = nullptr;
+    if (int rc = current_pipe(&p)) return rc;
+    p->want_slots = slots;
+    p->want_chunk_elems = chunk_elems;
     return B200V_OK;
 }
 
@@ -444,25 +471,30 @@ int b200v_vector_add_host(const float* hA, const float* hB, float* hC, size_t n)
 {
     B200V_REQUIRE(hA && hB && hC, B200V_ERR_INVALID, "NULL host array");
     if (n == 0) return B200V_OK;
-    int dev = 0;
-    B200V_CUDA(cudaGetDevice(&dev));
-    B200V_REQUIRE(dev >= 0 && dev < 64, B200V_ERR_INVALID, "device index %d out of range", dev);
-    HostPipe& p = g_pipe[dev];
+    HostPipe* pp = nullptr;
+    if (int rc = current_pipe(&pp)) return rc;
+    HostPipe& p = *pp;
     if (int rc = pipe_init(p)) return rc;
 
+    int rc = B200V_OK;
     size_t k = 0;
-    for (size_t off = 0; off < n; off += p.chunk_elems, ++k) {
-        const int slot = (int)(k % p.slots);
-        const size_t m = std::min(p.chunk_elems, n - off);
-        cudaStream_t st = p.stream[slot];
-        // stream order makes the slot's previous D2H finish before its buffers are overwritten
-        B200V_CUDA(cudaMemcpyAsync(p.a[slot], hA + off, m * sizeof(float), cudaMemcpyHostToDevice, st));
-        B200V_CUDA(cudaMemcpyAsync(p.b[slot], hB + off, m * sizeof(float), cudaMemcpyHostToDevice, st));
-        if (int rc = b200v_add_f32(p.c[slot], p.a[slot], p.b[slot], m, st)) return rc;
-        B200V_CUDA(cudaMemcpyAsync(hC + off, p.c[slot], m * sizeof(float), cudaMemcpyDeviceToHost, st));
+    for (size_t off = 0; off < n && rc == B200V_OK; off += p.chunk_elems, ++k)
+        rc = enqueue_chunk(p, (int)(k % p.slots), hA + off, hB + off, hC + off, std::min(p.chunk_elems, n - off));
+    // The call is synchronous on every path: whatever was queued — also before a failure — has finished
+    // with the caller's host buffers by the time it returns, so they may be freed or reused at once.
+    if (rc != B200V_OK) {
+        char first_error[sizeof g_err];
+        snprintf(first_error, sizeof first_error, "%s", g_err);
+        for (int i = 0; i < p.slots; ++i) (void)cudaStreamSynchronize(p.stream[i]);   // drain; the first error is the one reported
+        (void)cudaGetLastError();
+        snprintf(g_err, sizeof g_err, "%s", first_error);
+        return rc;
     }
-    for (int i = 0; i < p.slots; ++i) B200V_CUDA(cudaStreamSynchronize(p.stream[i]));
-    return B200V_OK;
+    for (int i = 0; i < p.slots; ++i) {
+        const cudaError_t e = cudaStreamSynchronize(p.stream[i]);
+        if (e != cudaSuccess && rc == B200V_OK) rc = cuda_status(e, "cudaStreamSynchronize (host pipeline)", __FILE__, __LINE__);
+    }
+    return rc;
 }
 
 int b200v_vector_add_host_release(void)

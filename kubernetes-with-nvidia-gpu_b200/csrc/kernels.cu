@@ -1,6 +1,6 @@
 // kernels.cu — device code of libb200v and the C-ABI entry points that launch it:
 // the streaming kernels (add/copy/scale/triad, fp32 + bf16), the index-hash fill, the
-// checksum reduction, and the peer-pull copy.  See include/b200v.h for the contract and the
+// checksum reduction, and the peer pull / peer push copies.  See include/b200v.h for the contract and the
 // reference lines each group stands in for.
 #include <cstdint>
 #include <cstring>
@@ -239,28 +239,47 @@ constexpr int kChecksumUnroll = 4;
 constexpr bool kChecksumTiled = true;   // 6870 vs 6683 GB/s read at 1 GiB (profiles/r01_tune_cksum.csv)
 
 // ------------------------------------------------------------------------------------------
-// peer pull: this device's SMs read a peer's buffer over NVLink with 256-bit loads (peer
-// addresses bypass the local L2, so no cache hint is asked for) and write local HBM.
+// peer pull / peer push: one GPU's SMs move a buffer across NVLink with 256-bit accesses.
+//   pull: the DESTINATION GPU runs the kernel: loads from the peer's address space, stores to local HBM.
+//         Every 32 bytes cost a read request going out and the data coming back, so under bidirectional
+//         load the requests share the link direction the other flow's data uses.
+//   push: the SOURCE GPU runs the kernel: loads from local HBM, stores into the peer's address space.
+//         Stores are posted: nothing travels back but acknowledgements, which is why the copy engine
+//         (which also pushes) keeps its rate when every GPU sends and receives at once.
+// Peer addresses bypass the local L2, so no cache hint is asked for.  Same body for both directions;
+// two entry kernels so a profile shows which one ran.
 
 constexpr int kPullBlock = 512;
 constexpr int kPullUnroll = 4;
 
-__global__ void __launch_bounds__(kPullBlock)
-peer_pull_kernel(Vec<32>* __restrict__ dst, const Vec<32>* __restrict__ src, size_t nvec)
+template <int BLOCK, int UNROLL>
+__device__ __forceinline__ void peer_move_body(Vec<32>* __restrict__ dst, const Vec<32>* __restrict__ src, size_t nvec)
 {
-    constexpr size_t TILE = (size_t)kPullBlock * kPullUnroll;
+    constexpr size_t TILE = (size_t)BLOCK * UNROLL;
     const size_t tiles = nvec / TILE;
     for (size_t t = blockIdx.x; t < tiles; t += gridDim.x) {
         const size_t base = t * TILE + threadIdx.x;
-        Vec<32> v[kPullUnroll];
+        Vec<32> v[UNROLL];
 #pragma unroll
-        for (int u = 0; u < kPullUnroll; ++u) v[u] = ldg<LD_DEFAULT>(src + base + (size_t)u * kPullBlock);
+        for (int u = 0; u < UNROLL; ++u) v[u] = ldg<LD_DEFAULT>(src + base + (size_t)u * BLOCK);
 #pragma unroll
-        for (int u = 0; u < kPullUnroll; ++u) stg<ST_DEFAULT>(dst + base + (size_t)u * kPullBlock, v[u]);
+        for (int u = 0; u < UNROLL; ++u) stg<ST_DEFAULT>(dst + base + (size_t)u * BLOCK, v[u]);
     }
     if (blockIdx.x == tiles % gridDim.x)
-        for (size_t i = tiles * TILE + threadIdx.x; i < nvec; i += kPullBlock)
+        for (size_t i = tiles * TILE + threadIdx.x; i < nvec; i += BLOCK)
             stg<ST_DEFAULT>(dst + i, ldg<LD_DEFAULT>(src + i));
+}
+
+__global__ void __launch_bounds__(kPullBlock)
+peer_pull_kernel(Vec<32>* __restrict__ dst, const Vec<32>* __restrict__ src, size_t nvec)
+{
+    peer_move_body<kPullBlock, kPullUnroll>(dst, src, nvec);
+}
+
+__global__ void __launch_bounds__(kPullBlock)
+peer_push_kernel(Vec<32>* __restrict__ peer_dst, const Vec<32>* __restrict__ local_src, size_t nvec)
+{
+    peer_move_body<kPullBlock, kPullUnroll>(peer_dst, local_src, nvec);
 }
 
 __global__ void __launch_bounds__(256)
@@ -481,14 +500,16 @@ int b200v_checksum_static(const void* d_buf, size_t nbytes, uint64_t word_offset
     return B200V_OK;
 }
 
-int b200v_peer_pull(void* d_local_dst, const void* d_peer_src, size_t bytes, void* stream)
+// Shared by pull and push: the 32-byte-aligned body goes through the 256-bit kernel, whatever is left
+// (an unaligned pair of pointers, or the last < 32 bytes) through the byte kernel.
+static int launch_peer_move(bool push, void* dst, const void* src, size_t bytes, void* stream)
 {
-    B200V_REQUIRE(d_local_dst && d_peer_src, B200V_ERR_INVALID, "NULL pointer");
+    B200V_REQUIRE(dst && src, B200V_ERR_INVALID, "NULL pointer");
     if (bytes == 0) return B200V_OK;
     int sms = 0;
     if (int rc = current_sm_count(&sms)) return rc;
     cudaStream_t st = as_stream(stream);
-    const bool aligned = (((uintptr_t)d_local_dst | (uintptr_t)d_peer_src) % 32) == 0;
+    const bool aligned = (((uintptr_t)dst | (uintptr_t)src) % 32) == 0;
     size_t body = aligned ? (bytes / 32) * 32 : 0;
     if (body) {
         size_t nvec = body / 32;
@@ -496,8 +517,12 @@ int b200v_peer_pull(void* d_local_dst, const void* d_peer_src, size_t bytes, voi
         size_t cap = (size_t)sms * 4;
         if (grid > cap) grid = cap;
         if (grid == 0) grid = 1;
-        peer_pull_kernel<<<(unsigned)grid, kPullBlock, 0, st>>>(reinterpret_cast<Vec<32>*>(d_local_dst),
-                                                               reinterpret_cast<const Vec<32>*>(d_peer_src), nvec);
+        if (push)
+            peer_push_kernel<<<(unsigned)grid, kPullBlock, 0, st>>>(reinterpret_cast<Vec<32>*>(dst),
+                                                                   reinterpret_cast<const Vec<32>*>(src), nvec);
+        else
+            peer_pull_kernel<<<(unsigned)grid, kPullBlock, 0, st>>>(reinterpret_cast<Vec<32>*>(dst),
+                                                                   reinterpret_cast<const Vec<32>*>(src), nvec);
         B200V_CUDA(cudaGetLastError());
     }
     if (body < bytes) {
@@ -505,11 +530,21 @@ int b200v_peer_pull(void* d_local_dst, const void* d_peer_src, size_t bytes, voi
         size_t grid = (rest + 255) / 256;
         size_t cap = (size_t)sms * 8;
         if (grid > cap) grid = cap;
-        byte_copy_kernel<<<(unsigned)grid, 256, 0, st>>>(reinterpret_cast<unsigned char*>(d_local_dst) + body,
-                                                        reinterpret_cast<const unsigned char*>(d_peer_src) + body, rest);
+        byte_copy_kernel<<<(unsigned)grid, 256, 0, st>>>(reinterpret_cast<unsigned char*>(dst) + body,
+                                                        reinterpret_cast<const unsigned char*>(src) + body, rest);
         B200V_CUDA(cudaGetLastError());
     }
     return B200V_OK;
+}
+
+int b200v_peer_pull(void* d_local_dst, const void* d_peer_src, size_t bytes, void* stream)
+{
+    return launch_peer_move(false, d_local_dst, d_peer_src, bytes, stream);
+}
+
+int b200v_peer_push(void* d_peer_dst, const void* d_local_src, size_t bytes, void* stream)
+{
+    return launch_peer_move(true, d_peer_dst, d_local_src, bytes, stream);
 }
 
 }  // extern "C"

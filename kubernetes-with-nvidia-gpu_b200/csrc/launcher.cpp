@@ -16,10 +16,11 @@
 //   gpu-validate --mode list           device discovery only (the nvidia-smi-style listing)
 //   gpu-validate --mode bench          STREAM copy/scale/add/triad sweep, fp32+bf16, + OpenMP baseline (configs[2])
 //   gpu-validate --mode node           one process per GPU, sharded triad, max over ranks       (configs[3])
-//   gpu-validate --mode p2p            all ordered GPU pairs: peer copy + peer-load kernel, verified (configs[4])
+//   gpu-validate --mode p2p            all ordered GPU pairs: peer copy, peer-load and peer-store kernels, verified (configs[4])
 //   gpu-validate --mode burnin         per-GPU triad burn-in, every pass verified               (configs[4])
 //   gpu-validate --mode full           burnin + p2p
 //   gpu-validate --mode host-reference the host loop alone (no GPU is touched or validated)
+//   gpu-validate --mode exit-codes     the status -> exit code table (no GPU is touched)
 #include "launcher_common.h"
 
 namespace gpuvalidate {
@@ -196,6 +197,28 @@ int mode_smoke(const Args& a)
     return pass();
 }
 
+// Prints how every library status maps to the pod's exit code and to the reference's troubleshooting
+// checklists (README:339-357).  No GPU is touched: this is how the mapping for hardware this pool does
+// not have (a non-sm_100 GPU -> 3, GPUs without peer access -> 5) is kept under test.
+int mode_exit_codes(const Args&)
+{
+    static const struct { int status; const char* hint; } rows[] = {
+        {B200V_OK, "pass"},
+        {B200V_ERR_INVALID, "internal/usage error"},
+        {B200V_ERR_NO_DEVICE, "README:353-357 'Pod Cannot Access GPU': check resources.limits nvidia.com/gpu, the container runtime, the driver"},
+        {B200V_ERR_CUDA, "CUDA runtime error: see the reason line"},
+        {B200V_ERR_ARCH, "the GPU is not a B200 (sm_100): this image carries sm_100a code only"},
+        {B200V_ERR_ALIGN, "internal/usage error"},
+        {B200V_ERR_PEER, "peer access between two GPUs is unavailable (NVLink/NVSwitch fabric, ACS, or the container's device set)"},
+        {B200V_ERR_MISMATCH, "GPU result differs from the host loop"},
+        {B200V_ERR_NOMEM, "device or pinned-host allocation failed"},
+    };
+    for (const auto& r : rows)
+        printf("status %d %-19s -> exit %d  (%s)\n", r.status, b200v_status_name(r.status), exit_code_for(r.status), r.hint);
+    printf("usage error             -> exit %d\n", EX_USAGE_ERR);
+    return EX_PASS;
+}
+
 int mode_list(const Args&)
 {
     int count = 0;
@@ -261,7 +284,7 @@ double now_s()
 void usage()
 {
     fprintf(stderr,
-            "usage: gpu-validate [--mode smoke|list|bench|node|p2p|burnin|full|host-reference]\n"
+            "usage: gpu-validate [--mode smoke|list|bench|node|p2p|burnin|full|host-reference|exit-codes]\n"
             "                    [--device D] [--gpus G] [--n N | --log2n K] [--dtype f32|bf16] [--op add|copy|scale|triad]\n"
             "                    [--iters I] [--warmup W] [--seconds S] [--seed X] [--p2p-bytes B]\n"
             "                    [--min-log2-bytes a --max-log2-bytes b] [--measured-copy-gbs G] [--json FILE] [--inject-fault] [--fail-on-throttle]\n"
@@ -331,6 +354,7 @@ int main(int argc, char** argv)
     }
     if (a.mode == "smoke") return mode_smoke(a);
     if (a.mode == "list") return mode_list(a);
+    if (a.mode == "exit-codes") return mode_exit_codes(a);
     if (a.mode == "host-reference") return mode_host_reference(a);
     if (a.mode == "bench") return mode_bench(a);
     if (a.mode == "node") return mode_node(a, false, true);

@@ -95,6 +95,7 @@ double now_s();
 // modes (launcher.cpp: smoke, list, host-reference; mode_bench.cpp; mode_node.cpp; mode_p2p.cpp)
 int mode_smoke(const Args& a);
 int mode_list(const Args& a);
+int mode_exit_codes(const Args& a);
 int mode_host_reference(const Args& a);
 int mode_bench(const Args& a);
 int mode_node(const Args& a, bool burnin, bool print_verdict);

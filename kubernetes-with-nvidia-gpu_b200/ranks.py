@@ -18,6 +18,7 @@ class Ranks:
         self.dist = None
         self.torch = None
         self.device = "cpu"
+        self.host_group = None
         if self.world > 1:
             import torch
             import torch.distributed as dist
@@ -28,6 +29,9 @@ class Ranks:
                 torch.cuda.set_device(self.local_rank)
                 self.device = f"cuda:{self.local_rank}"
                 dist.init_process_group("nccl", device_id=torch.device(self.device))
+                # a second, CPU-only group for waits that must not put a kernel on the GPUs (an NCCL barrier
+                # parks a spinning kernel on every waiting rank's device)
+                self.host_group = dist.new_group(backend="gloo")
             else:
                 dist.init_process_group(backend)
 
@@ -37,6 +41,12 @@ class Ranks:
             self.dist.barrier()
         if self.device_sync is not None:
             self.device_sync()
+
+    def host_barrier(self):
+        """Wait for every rank on the host only: no GPU work is enqueued anywhere while ranks wait.
+        Used while rank 0 runs the product's launcher binaries on all the GPUs."""
+        if self.dist is not None:
+            self.dist.barrier(group=self.host_group) if self.host_group is not None else self.dist.barrier()
 
     def _reduce(self, values, op, dtype):
         if self.dist is None:

@@ -31,11 +31,39 @@ def test_reference_arm_line():
     assert cb["kind"] == "port" and cb["cores"] >= 1 and cb["value"] == d["value"] and "2^" in cb["sample"]
     assert "workload" in d["config"] and "model" not in d["config"]
     assert d["value"] > 0.5 and d["gpu_launches"] == 0
+    # both arms print the SAME config object for the same N (it names the workload, nothing arm-specific)
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("bench_mod", os.path.join(ROOT, "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    assert d["config"] == bench.workload_config(1)
+    assert bench.workload_config(8)["parallelism"].startswith("shard8")
+
+
+def test_oracle_shard_checksums_add_up():
+    """The N > 1 parity leg: every rank checks its own global index range; the shards' checksums add up to the
+    whole vector's, and a chunked walk equals a one-shot one."""
+    import importlib.util
+    import oracle_lib as O
+    spec = importlib.util.spec_from_file_location("bench_mod", os.path.join(ROOT, "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    n, world = 300_007, 3
+    x = O.fill("f32", 0, n, bench.SEED, 0)
+    y = O.fill("f32", 0, n, bench.SEED, 1)
+    for op in ("add", "triad"):
+        whole = O.checksum(O.op(op, "f32", n, s=3.0, x=x, y=y))
+        parts = [0, 0]
+        for r in range(world):
+            b, c = r * n // world, (r + 1) * n // world - r * n // world
+            ck = bench.oracle_shard_checksum(op, b, c, b, threads=2, chunk=1 << 15)
+            parts = [(parts[0] + ck[0]) & bench.M64, (parts[1] + ck[1]) & bench.M64]
+        assert tuple(parts) == whole
 
 
 @pytest.mark.gpu
 def test_our_arm_line():
-    d = run_bench("--steps", "30", "--warmup", "3", "--e2e-steps", "2")
+    d = run_bench("--steps", "30", "--warmup", "3", "--e2e-steps", "2", "--sustained-seconds", "0.5", timeout=900)
     assert BASE_KEYS <= set(d) and "impl" not in d
     assert d["metric"].startswith("vectorAdd/triad HBM GB/s") and d["scaling"] == "weak" and d["data"] == "synthetic"
     assert d["n_gpus"] == 1 and d["steps"] == 30 and d["gpu_launches"] == 30
@@ -52,4 +80,20 @@ def test_our_arm_line():
     assert d["parity"]["job_checksum"] == d["cpu_baseline"]["output_checksum"]
     assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] >= 1
     assert "sm_mhz" in d["clocks"] and "reasons" in d["clocks"]
-    assert "workload" in d["config"] and "model" not in d["config"]
+    assert "workload" in d["config"] and "model" not in d["config"] and "gpu" not in d["config"]
+    assert d["device"]["gpu"] == "NVIDIA B200" and d["device"]["sm_count"] == 148
+    # sustained: back-to-back launches for the asked time, within a few % of the K-step value, clocks over that window
+    su = d["sustained"]
+    for k in ("add", "triad"):
+        assert su[k]["seconds"] >= 0.45 and su[k]["launches_per_gpu"] > 500 and 0.9 < su[k]["gbs"] / d["value"] < 1.1
+        assert su[k]["clocks"]["samples"] >= 10 and su[k]["clocks"]["power_w_max"] > 200
+    assert su["gbs"] == su["add"]["gbs"]
+    # configs[3]: 2^32-element triad (one shard at N = 1), device checksum == the oracle's
+    sh = d["triad_sharded_2p32"]
+    assert sh["elements_total"] == 1 << 32 and sh["matches_oracle"] is True and sh["scaling"] == "strong"
+    assert 3000 < sh["node_gbs"] < 12000
+    # the product's own shard launcher, run by the bench as a subprocess
+    nn = d["native_node"]
+    assert nn["ok"] and nn["verified"] and nn["verdict"] == "Test PASSED" and nn["elements"] == 1 << 32 and nn["gpus"] == 1
+    assert nn["node_gbs_from"] == "max over ranks of mean ms" and 3000 < nn["node_gbs"] < 12000
+    assert d["p2p"] is None          # one GPU: no pair to check

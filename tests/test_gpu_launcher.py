@@ -18,8 +18,11 @@ def exe():
     return pkg.LAUNCHER_PATH
 
 
-def run(exe, *args, timeout=600):
-    return subprocess.run([exe, *args], capture_output=True, text=True, timeout=timeout)
+def run(exe, *args, timeout=600, env=None):
+    e = dict(os.environ)
+    if env:
+        e.update(env)
+    return subprocess.run([exe, *args], capture_output=True, text=True, timeout=timeout, env=e)
 
 
 def last_line(r):
@@ -61,6 +64,19 @@ def test_missing_device_index(exe):
     assert r.returncode == 2 and last_line(r) == "Test FAILED"
 
 
+def test_no_gpu_granted_on_a_gpu_box(exe):
+    """A pod scheduled without `nvidia.com/gpu` in its limits (or with a broken runtime hook) sees no device even
+    on a GPU node: exit 2, Test FAILED, and the hint that points at the reference's 'Pod Cannot Access GPU'
+    checklist (reference README.md:353-357)."""
+    for mode in ([], ["--mode", "list"], ["--mode", "node", "--log2n", "20"], ["--mode", "p2p"]):
+        r = run(exe, *mode, env={"CUDA_VISIBLE_DEVICES": ""})
+        assert r.returncode == 2, (mode, r.stdout + r.stderr)
+        assert last_line(r) == "Test FAILED" and "Test PASSED" not in r.stdout
+    r = run(exe, env={"CUDA_VISIBLE_DEVICES": ""})
+    assert "no usable CUDA device" in r.stdout
+    assert "nvidia.com/gpu in the pod's resources.limits" in r.stdout and "NVIDIA container runtime" in r.stdout
+
+
 def test_list_mode(exe):
     r = run(exe, "--mode", "list")
     assert r.returncode == 0
@@ -89,6 +105,11 @@ def test_node_mode_one_gpu(exe, tmp_path):
     assert r.returncode == 0 and last_line(r) == "Test PASSED", r.stdout + r.stderr
     d = json.load(open(js))
     assert d["ok"] and d["gpus"] == 1 and d["elements"] == 1 << 28 and d["node_gbs"] > 4000
+    # the node figure is the max-over-ranks MEAN (a common timed window); best single launches come second
+    assert d["node_gbs_from"] == "max over ranks of mean ms"
+    assert abs(d["node_gbs"] - 12 * (1 << 28) / d["max_mean_ms"] * 1e-6) < 1.0
+    assert d["node_best_gbs"] >= d["node_gbs"] * 0.99
+    assert re.search(r"\[node\] 1 GPU: [\d.]+ GB/s \(bytes / max over ranks of mean ms", r.stdout)
 
 
 @pytest.mark.parametrize("op,dtype", [("add", "bf16"), ("copy", "f32"), ("scale", "bf16"), ("triad", "bf16")])
@@ -101,6 +122,16 @@ def test_node_mode_other_ops(exe, op, dtype):
 def test_node_mode_fault_injection(exe):
     r = run(exe, "--mode", "node", "--gpus", "1", "--log2n", "24", "--iters", "2", "--inject-fault")
     assert r.returncode == 1 and last_line(r) == "Test FAILED"
+    # the fault is a flipped bit in the device output: the checksum comparison itself must have caught it
+    assert "flipped the low bit of output word" in r.stdout and "FAILED" in r.stdout
+
+
+def test_node_mode_odd_bf16_shards_cover_every_element(exe, tmp_path):
+    """3 ranks' worth of a bf16 vector whose shards begin on odd indices: nothing is dropped at the seams."""
+    js = tmp_path / "node.json"
+    r = run(exe, "--mode", "node", "--gpus", "1", "--n", "30000001", "--iters", "2", "--dtype", "bf16", "--json", str(js))
+    assert r.returncode == 0 and last_line(r) == "Test PASSED", r.stdout + r.stderr
+    assert json.load(open(js))["elements"] == 30000001
 
 
 def test_burnin_mode_verifies_every_pass(exe, tmp_path):
@@ -192,10 +223,14 @@ def test_p2p_all_pairs(exe, tmp_path):
     assert r.returncode == 0 and last_line(r) == "Test PASSED", r.stdout + r.stderr
     d = json.load(open(js))
     assert d["ok"] and len(d["pairs"]) == g * (g - 1)
-    assert all(p["memcpy_peer_gbs"] > 100 and p["peer_load_gbs"] > 100 for p in d["pairs"]), d["pairs"]
-    assert len(d["concurrent_shift_gbs_per_gpu"]) == g - 1 and min(d["concurrent_shift_gbs_per_gpu"]) > 100
-    assert len(d["concurrent_shift_push_gbs_per_gpu"]) == g - 1 and min(d["concurrent_shift_push_gbs_per_gpu"]) > 100
-    assert "concurrent rounds" in r.stdout
+    assert all(p["memcpy_peer_gbs"] > 100 and p["peer_load_gbs"] > 100 and p["peer_store_gbs"] > 100 for p in d["pairs"]), d["pairs"]
+    for key in ("concurrent_shift_gbs_per_gpu", "concurrent_shift_push_gbs_per_gpu", "concurrent_shift_push_kernel_gbs_per_gpu"):
+        assert len(d[key]) == g - 1 and min(d[key]) > 100, key
+    assert "concurrent rounds" in r.stdout and "peer-store" in r.stdout
+    s = d["summary"]
+    for key in ("memcpy_peer", "peer_load", "peer_store", "concurrent_memcpy_peer", "concurrent_peer_load", "concurrent_peer_store"):
+        assert 100 < s[key]["min"] <= s[key]["median"] <= s[key]["max"] and 0 < s[key]["frac_of_nvlink_at_median"] < 1.1, key
+    assert d["nvlink_gbs_per_direction"] == 900
 
 
 @multi
@@ -227,6 +262,28 @@ def test_peer_entry_points_through_the_abi():
     pkg.check(L.b200v_peer_pull(C.c_void_p(dst.ptr), C.c_void_p(src.ptr), 4 * n, None))
     np.testing.assert_array_equal(dst.download(np.uint32, n), want)
     assert pkg.checksum(C.c_void_p(dst.ptr), 4 * n) == O.checksum(want)
+    # push: the SOURCE GPU's kernel stores into the peer's buffer (aligned body + ragged tail, then an
+    # unaligned pair of pointers, which goes through the byte path)
+    pkg.check(L.b200v_memset(C.c_void_p(dst.ptr), 0, 4 * n, None))
+    pkg.check(L.b200v_device_sync())
+    pkg.check(L.b200v_set_device(0))
+    pkg.check(L.b200v_peer_push(C.c_void_p(dst.ptr), C.c_void_p(src.ptr), 4 * n, None))
+    pkg.check(L.b200v_device_sync())
+    pkg.check(L.b200v_set_device(1))
+    np.testing.assert_array_equal(dst.download(np.uint32, n), want)
+    assert pkg.checksum(C.c_void_p(dst.ptr), 4 * n) == O.checksum(want)
+    pkg.check(L.b200v_memset(C.c_void_p(dst.ptr), 0, 4 * n, None))
+    pkg.check(L.b200v_device_sync())
+    pkg.check(L.b200v_set_device(0))
+    pkg.check(L.b200v_peer_push(dst.at(4), src.at(8), 4 * (n - 2) - 1, None))
+    pkg.check(L.b200v_device_sync())
+    assert L.b200v_peer_push(None, C.c_void_p(src.ptr), 16, None) == pkg.ERR_INVALID
+    pkg.check(L.b200v_peer_push(C.c_void_p(dst.ptr), C.c_void_p(src.ptr), 0, None))
+    pkg.check(L.b200v_set_device(1))
+    got = dst.download(np.uint8, 4 * n)
+    wb = want.view(np.uint8)
+    assert not got[:4].any() and not got[4 + 4 * (n - 2) - 1:].any()
+    np.testing.assert_array_equal(got[4:4 + 4 * (n - 2) - 1], wb[8:8 + 4 * (n - 2) - 1])
     dst.free()
     pkg.check(L.b200v_set_device(0))
     src.free()

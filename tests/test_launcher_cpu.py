@@ -91,11 +91,53 @@ def test_host_reference_fault_injection_turns_the_verdict(exe):
 
 
 def test_launcher_is_self_contained(exe):
-    """The image only gets driver libraries from the container runtime: no libcudart, no oracle."""
+    """The image is a base plus this ONE file (reference README.md:312-314's slot): beyond glibc the
+    binary may need nothing the image would have to install — no libcudart, libstdc++, libgomp,
+    libb200v or oracle — because only driver libraries arrive from the container runtime."""
     ldd = subprocess.run(["ldd", exe], capture_output=True, text=True).stdout
-    assert "libcudart" not in ldd and "liboracle" not in ldd and "libstdc++" not in ldd and "libb200v" not in ldd
+    needed = {ln.split()[0] for ln in ldd.strip().splitlines()}
+    allowed = re.compile(r"^(linux-vdso\.so\.1|libc\.so\.6|libm\.so\.6|libdl\.so\.2|libpthread\.so\.0|librt\.so\.1|/lib64/ld-linux-x86-64\.so\.2)$")
+    extra = sorted(n for n in needed if not allowed.match(n))
+    assert not extra, f"gpu-validate needs libraries a bare glibc image does not have: {extra}"
     archs = set(re.findall(r"sm_\d+a?", subprocess.run(["cuobjdump", "-lelf", exe], capture_output=True, text=True).stdout))
     assert archs == {"sm_100a"}
+
+
+def test_dockerfile_is_base_plus_one_file(exe):
+    """The image recipe installs nothing: FROM, one COPY of the built binary, ENTRYPOINT == the pod's command."""
+    deploy = os.path.join(ROOT, "kubernetes-with-nvidia-gpu_b200", "deploy")
+    lines = [ln.strip() for ln in open(os.path.join(deploy, "Dockerfile")) if ln.strip() and not ln.startswith("#")]
+    verbs = [ln.split()[0] for ln in lines]
+    assert verbs.count("FROM") == 1 and verbs.count("COPY") == 1 and "RUN" not in verbs and "ADD" not in verbs, lines
+    copy = next(ln for ln in lines if ln.startswith("COPY")).split()
+    src, dst = copy[1], copy[2]
+    assert os.path.samefile(os.path.join(ROOT, src), exe), "the Dockerfile copies something other than the built launcher"
+    entry = next(ln for ln in lines if ln.startswith("ENTRYPOINT"))
+    entrypoint = yaml.safe_load(entry[len("ENTRYPOINT"):])
+    assert entrypoint == [dst]
+    pod = yaml.safe_load(open(os.path.join(deploy, "pod-cuda-vector-add.yaml")))
+    job = yaml.safe_load(open(os.path.join(deploy, "job-node-validate.yaml")))
+    assert pod["spec"]["containers"][0]["command"] == entrypoint
+    assert job["spec"]["template"]["spec"]["containers"][0]["command"] == entrypoint
+    tag = re.search(r"-t (\S+)", open(os.path.join(deploy, "Dockerfile")).read()).group(1)
+    assert pod["spec"]["containers"][0]["image"] == tag == job["spec"]["template"]["spec"]["containers"][0]["image"]
+
+
+def test_exit_code_table(exe):
+    """Every library status maps to a distinct, documented pod exit code — including the two that need
+    hardware this pool does not have (not sm_100 -> 3; no peer access -> 5): reference README.md:353-357's
+    'Pod Cannot Access GPU' checklist is what exit 2 points at."""
+    r = run(exe, "--mode", "exit-codes")
+    assert r.returncode == 0
+    table = {m.group(1): int(m.group(2)) for m in re.finditer(r"status \d+ (B200V_\w+)\s+-> exit (\d+)", r.stdout)}
+    assert table == {"B200V_OK": 0, "B200V_ERR_INVALID": 4, "B200V_ERR_NO_DEVICE": 2, "B200V_ERR_CUDA": 4, "B200V_ERR_ARCH": 3,
+                     "B200V_ERR_ALIGN": 4, "B200V_ERR_PEER": 5, "B200V_ERR_MISMATCH": 1, "B200V_ERR_NOMEM": 4}
+    assert "usage error             -> exit 64" in r.stdout
+    assert "Test PASSED" not in r.stdout and "Test FAILED" not in r.stdout      # a table, not a verdict
+    integration = open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    for name, code in table.items():
+        if name in ("B200V_ERR_ARCH", "B200V_ERR_PEER", "B200V_ERR_NO_DEVICE", "B200V_ERR_MISMATCH"):
+            assert re.search(rf"\b{code}\b", integration)
 
 
 def test_pod_manifest_keeps_the_reference_envelope():

@@ -25,6 +25,7 @@ WORKER = textwrap.dedent("""
     out = O.op("triad", "f32", count, s=3.0, x=x, y=y)
     total = R.sum_checksums(O.checksum(out, begin))
     R.barrier()
+    R.host_barrier()                                            # the CPU-only wait (rank 0 runs the launcher binaries meanwhile)
     slowest = R.max(10.0 + R.rank)                              # stands in for per-rank device ms
     ok_all = R.all_ok(True)
     ok_one_bad = R.all_ok(R.rank != 1)

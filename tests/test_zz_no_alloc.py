@@ -6,7 +6,10 @@ the GPU, a hook that must not call cudaMalloc/cudaFree because they synchronise 
 them the library carries the reduction's scratch inside its own image.  This test calls that entry
 point through the C ABI and requires exactly the result of the ordinary b200v_checksum (which gets
 a caller-allocated workspace) — bit for bit, the tolerance every test here uses — on two calls in
-a row, because the second call finds the first call's leftovers in the shared array.
+a row, because the second call finds the first call's leftovers in the shared array.  The small
+buffer is also brought back to the host and summed by the CPU oracle, so the two CUDA entry points
+cannot agree on a shared mistake.  A second case repeats this on GPU 1 after GPU 0 where the box has
+two GPUs: every device holds its own copy of the array, found through its own address look-up.
 It stands alone (fresh process) and also runs after every other GPU test.
 """
 import ctypes as C
@@ -14,6 +17,7 @@ import ctypes as C
 import numpy as np
 import pytest
 
+import oracle_lib as O
 from b200v_pkg import pkg
 
 pytestmark = pytest.mark.gpu
@@ -47,6 +51,9 @@ def test_static_scratch_checksum_matches_workspace_checksum_twice_in_a_row():
     want_small = pkg.checksum(small.at(4), 4 * n_small + 3, 77)
     assert (int(got[0]), int(got[1])) == want_big
     assert (int(got[2]), int(got[3])) == want_small
+    # ... and what the CPU oracle says about the same bytes, copied back to the host
+    host_bytes = small.download(np.uint8, 4 * n_small + 3, byte_offset=4)
+    assert want_small == O.checksum(host_bytes, 77)
 
     # and again in the other order: the array now holds the small call's partials
     static_sum(small.at(4), 4 * n_small + 3, 77, 0)
@@ -65,3 +72,29 @@ def test_static_scratch_checksum_matches_workspace_checksum_twice_in_a_row():
     pkg.check(L.b200v_device_sync())
     for b in (big, small, out):
         b.free()
+
+
+@pytest.mark.multigpu
+def test_static_scratch_is_per_device():
+    """GPU 0 first, then GPU 1, then GPU 0 again: each device resolves and keeps its own array address."""
+    if pkg.device_count() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    L = pkg.lib()
+    vp = C.c_void_p
+    n = (3 << 20) + 5
+    want = None
+    for dev in (0, 1, 0):
+        pkg.check(L.b200v_set_device(dev))
+        buf = pkg.DeviceBuffer(4 * n)
+        out = pkg.DeviceBuffer(16)
+        pkg.check(L.b200v_fill(pkg.F32, vp(buf.ptr), 123, n, SEED, 11, pkg.GEN_BITS, None))
+        for _ in range(2):                                   # twice in a row on this device
+            pkg.check(L.b200v_checksum_static(vp(buf.ptr), 4 * n, 9, vp(out.ptr), None))
+            got = tuple(int(x) for x in out.download(np.uint64, 2))
+            assert got == pkg.checksum(vp(buf.ptr), 4 * n, 9)
+            if want is None:
+                want = O.checksum(buf.download(np.uint32, n), 9)
+            assert got == want                               # same data on every device: same sum, oracle-checked
+        buf.free()
+        out.free()
+    pkg.check(L.b200v_set_device(0))
