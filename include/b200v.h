@@ -98,6 +98,10 @@ B200V_API int b200v_malloc(void **dptr, size_t bytes);
 B200V_API int b200v_free(void *dptr);
 B200V_API int b200v_host_alloc(void **hptr, size_t bytes);      /* pinned */
 B200V_API int b200v_host_free(void *hptr);
+/* pin host memory the caller already owns (malloc, mmap, a numpy array), in place, so that copies
+ * from / to it run at PCIe speed without a staging pass; undo with b200v_host_unregister before freeing it */
+B200V_API int b200v_host_register(void *hptr, size_t bytes);
+B200V_API int b200v_host_unregister(void *hptr);
 B200V_API int b200v_memcpy_h2d(void *dptr, const void *hptr, size_t bytes, void *stream);
 B200V_API int b200v_memcpy_d2h(void *hptr, const void *dptr, size_t bytes, void *stream);
 /* the driver's own device-to-device copy: the same-box comparator the sweep prints beside the kernels */

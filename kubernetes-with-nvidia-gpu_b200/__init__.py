@@ -86,6 +86,8 @@ def _signatures():
         "b200v_free": (i32, [vp]),
         "b200v_host_alloc": (i32, [pvp, sz]),
         "b200v_host_free": (i32, [vp]),
+        "b200v_host_register": (i32, [vp, sz]),
+        "b200v_host_unregister": (i32, [vp]),
         "b200v_memcpy_h2d": (i32, [vp, vp, sz, vp]),
         "b200v_memcpy_d2h": (i32, [vp, vp, sz, vp]),
         "b200v_memcpy_d2d": (i32, [vp, vp, sz, vp]),

@@ -213,6 +213,19 @@ int b200v_host_free(void* hptr)
     return B200V_OK;
 }
 
+int b200v_host_register(void* hptr, size_t bytes)
+{
+    B200V_REQUIRE(hptr != nullptr && bytes > 0, B200V_ERR_INVALID, "NULL or empty host range");
+    B200V_CUDA(cudaHostRegister(hptr, bytes, cudaHostRegisterPortable));
+    return B200V_OK;
+}
+
+int b200v_host_unregister(void* hptr)
+{
+    if (hptr) B200V_CUDA(cudaHostUnregister(hptr));
+    return B200V_OK;
+}
+
 int b200v_memcpy_h2d(void* dptr, const void* hptr, size_t bytes, void* stream)
 {
     if (bytes == 0) return B200V_OK;

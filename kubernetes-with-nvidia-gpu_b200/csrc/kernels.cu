@@ -248,6 +248,15 @@ constexpr bool kChecksumTiled = true;   // 6870 vs 6683 GB/s read at 1 GiB (prof
 //         (which also pushes) keeps its rate when every GPU sends and receives at once.
 // Peer addresses bypass the local L2, so no cache hint is asked for.  Same body for both directions;
 // two entry kernels so a profile shows which one ran.
+//
+// Measured (tools/tune_p2p.cu, profiles/r02_tune_p2p_2gpu.csv, 1 GiB, GPU0 <-> GPU1), one way / both ways at once:
+//   copy engine 779 / 773   pull 784 / 672   push 714 / 705 GB/s per direction.
+// Every SM-issued store variant lands on the same 714 / 704: 128- or 256-bit, any unroll / block / grid, .cs and
+// no-allocate / evict-first hints, and the bulk-copy engine (cp.async.bulk shared -> peer global, 4..64 KiB tiles,
+// 2..4 stages, 1..8 CTAs per SM).  The ceiling is the write packets SMs (and TMA) emit on NVLink, not the kernel:
+// the copy engine's writes carry more payload per packet.  So: push is the better KERNEL when traffic is
+// bidirectional (+5.5 % over pull), pull the better one for a one-way transfer, and cudaMemcpyPeer beats both
+// when both directions are busy.
 
 constexpr int kPullBlock = 512;
 constexpr int kPullUnroll = 4;
@@ -513,9 +522,10 @@ static int launch_peer_move(bool push, void* dst, const void* src, size_t bytes,
     size_t body = aligned ? (bytes / 32) * 32 : 0;
     if (body) {
         size_t nvec = body / 32;
+        // one 64 KiB tile per CTA, like the streaming kernels (profiles/r02_tune_p2p_2gpu.csv: pull 784 / 672 GB/s
+        // one way / both ways against 777 / 667 for 4 CTAs per SM; push is 713 / 704 either way)
         size_t grid = nvec / ((size_t)kPullBlock * kPullUnroll);
-        size_t cap = (size_t)sms * 4;
-        if (grid > cap) grid = cap;
+        if (grid > 0x7FFFFFFFull) grid = 0x7FFFFFFFull;
         if (grid == 0) grid = 1;
         if (push)
             peer_push_kernel<<<(unsigned)grid, kPullBlock, 0, st>>>(reinterpret_cast<Vec<32>*>(dst),

@@ -1,26 +1,30 @@
 #!/usr/bin/env python3
 """What bounds the end-to-end (host-buffer) vectorAdd at N GPUs of one box?
 
-    python tools/e2e_scaling.py out.json                                  # N = 1
-    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
-        --master-port P tools/e2e_scaling.py out.json                     # N ranks, one per GPU
+    python tools/e2e_scaling.py out.json                                  # one GPU
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node W --master-addr 127.0.0.1 \
+        --master-port P tools/e2e_scaling.py out.json                     # W ranks, one per GPU
 
-Every rank drives its own GPU; all ranks start each measurement together (gloo barrier on the host, so
-no kernel is parked on any GPU) and the job's time is the max over ranks of the wall time.  Measured:
+One launch with W ranks measures every N in {1, 2, 4, 8} <= W: for a given N only ranks 0..N-1 are
+active, the others idle at the barriers (gloo, on the host: no kernel is parked on any GPU).  All active
+ranks start each measurement together; the job's time is the max over ranks of the wall time.
 
   raw      pinned H2D alone, D2H alone, both directions at once, and the step's own mix (2 GiB in while
-           1 GiB goes out) — per GPU and summed over the N GPUs: the PCIe / root-complex ceiling;
-  host     what the host's DRAM gives the same cores: every rank copying 1 GiB with its share of the
-           host threads (the oracle's OpenMP copy loop) at the same time: the host-DRAM ceiling;
-  pipeline b200v_vector_add_host over chunk size x slots, N ranks at once: the e2e number itself;
-  bound    per N: the step's bytes through the lower of the two ceilings.
+           1 GiB goes out) — per GPU and summed over the N GPUs: what the copy engines / PCIe / root
+           complex deliver with no kernel and no pipeline in the way;
+  solo     each GPU alone, in turn (is every GPU's link the same?);
+  pairs    GPU 0 together with each other GPU (which GPUs share an upstream path?);
+  host     what the host's DRAM gives the CPU: all W ranks copying 1 GiB at once with their share of the
+           host threads (the oracle's OpenMP copy / add loops, used here only as a bandwidth probe);
+  pipeline b200v_vector_add_host over chunk size x slots with N ranks at once: the e2e number itself,
+           with cudaHostAlloc buffers and, once, with transparent-huge-page-backed registered buffers.
 
-Developer tool (evidence under profiles/r02_e2e_scaling*.json); not part of the product.  The oracle's copy
-loop is used here only as a host memory-bandwidth probe.
+Developer tool (evidence: profiles/r02_e2e_scaling*.json); not part of the product.
 """
 import ctypes as C
 import importlib
 import json
+import mmap
 import os
 import subprocess
 import sys
@@ -53,17 +57,19 @@ def sync():
     pkg.check(L.b200v_device_sync())
 
 
-def job_seconds(fn, reps=3):
-    """All ranks run fn at the same time; returns the best-of-reps of (max over ranks of the wall time)."""
-    fn()
-    sync()
+def job_seconds(fn, active=True, reps=3):
+    """Active ranks run fn at the same time; returns best-of-reps of (max over ranks of the wall time)."""
+    if active:
+        fn()
+        sync()
     best = 1e9
     for _ in range(reps):
         R.barrier()
         t0 = time.perf_counter()
-        fn()
-        sync()
-        dt = R.max(time.perf_counter() - t0)
+        if active:
+            fn()
+            sync()
+        dt = R.max(time.perf_counter() - t0 if active else 0.0)
         best = min(best, dt)
     return best
 
@@ -77,14 +83,13 @@ s1, s2 = vp(None), vp(None)
 pkg.check(L.b200v_stream_create(C.byref(s1)))
 pkg.check(L.b200v_stream_create(C.byref(s2)))
 
-out = {"n_gpus": world, "host_cores": cores, "host_threads_per_rank": threads, "bytes_per_array": GIB}
+out = {"ranks_launched": world, "host_cores": cores, "host_threads_per_rank": threads, "bytes_per_array": GIB}
 
 # ---- topology, as far as the box shows it ---------------------------------------------------------
 if rank == 0:
     topo = {}
     try:
-        nodes = sorted(d for d in os.listdir("/sys/devices/system/node") if d.startswith("node"))
-        topo["numa_nodes"] = nodes
+        topo["numa_nodes"] = sorted(d for d in os.listdir("/sys/devices/system/node") if d.startswith("node"))
     except Exception as e:
         topo["numa_nodes"] = repr(e)
     gpus = []
@@ -100,16 +105,19 @@ if rank == 0:
         gpus.append(entry)
     topo["gpus"] = gpus
     try:
-        topo["lscpu"] = [ln for ln in subprocess.run(["lscpu"], capture_output=True, text=True).stdout.splitlines()
+        topo["lscpu"] = [ln.strip() for ln in subprocess.run(["lscpu"], capture_output=True, text=True).stdout.splitlines()
                          if any(k in ln for k in ("Model name", "Socket", "NUMA", "CPU(s):", "Thread", "Hypervisor", "L3"))]
     except Exception:
         pass
     try:
-        mem = {ln.split(":")[0]: ln.split(":")[1].strip() for ln in open("/proc/meminfo") if ln.startswith(("MemTotal", "MemAvailable", "Hugepagesize"))}
-        topo["meminfo"] = mem
+        topo["meminfo"] = {ln.split(":")[0]: ln.split(":")[1].strip() for ln in open("/proc/meminfo")
+                           if ln.startswith(("MemTotal", "MemAvailable", "Hugepagesize", "AnonHugePages"))}
+        topo["thp"] = open("/sys/kernel/mm/transparent_hugepage/enabled").read().strip()
     except Exception:
         pass
     out["topology"] = topo
+    print("topology", json.dumps(topo), flush=True)
+
 
 # ---- raw copies --------------------------------------------------------------------------------------
 def h2d():
@@ -131,21 +139,69 @@ def step_mix():          # the step's own traffic: 2 GiB in (two arrays) while 1
     pkg.check(L.b200v_memcpy_d2h(vp(hC.ptr), vp(dZ.ptr), GIB, s2))
 
 
-raw = {}
-t = job_seconds(h2d)
-raw["h2d_gbs_per_gpu"], raw["h2d_gbs_sum"] = GIB / t * 1e-9, world * GIB / t * 1e-9
-t = job_seconds(d2h)
-raw["d2h_gbs_per_gpu"], raw["d2h_gbs_sum"] = GIB / t * 1e-9, world * GIB / t * 1e-9
-t = job_seconds(both)
-raw["bidir_each_gbs_per_gpu"], raw["bidir_total_gbs_sum"] = GIB / t * 1e-9, 2 * world * GIB / t * 1e-9
-t = job_seconds(step_mix)
-raw["step_mix_ms"] = t * 1e3
-raw["step_mix_e2e_bound_gbs_sum"] = world * 12 * N / t * 1e-9      # 12 B/element through the copy engines alone
-out["raw"] = raw
-if rank == 0:
-    print("raw", json.dumps(raw), flush=True)
+def pipeline_call(a=hA, b=hB, c=hC):
+    pkg.check(L.b200v_vector_add_host(vp(a.ptr), vp(b.ptr), vp(c.ptr), N))
 
-# ---- host DRAM: every rank copies 1 GiB with its share of the host threads, all at once ----------------
+
+def raw_block(active, m):
+    r = {}
+    t = job_seconds(h2d, active)
+    r["h2d_gbs_per_gpu"], r["h2d_gbs_sum"] = GIB / t * 1e-9, m * GIB / t * 1e-9
+    t = job_seconds(d2h, active)
+    r["d2h_gbs_per_gpu"], r["d2h_gbs_sum"] = GIB / t * 1e-9, m * GIB / t * 1e-9
+    t = job_seconds(both, active)
+    r["bidir_each_gbs_per_gpu"], r["bidir_total_gbs_sum"] = GIB / t * 1e-9, 2 * m * GIB / t * 1e-9
+    t = job_seconds(step_mix, active)
+    r["step_mix_ms"] = t * 1e3
+    r["step_mix_e2e_bound_gbs_sum"] = m * 12 * N / t * 1e-9      # 12 B/element through the copy engines alone
+    return r
+
+
+sizes = [m for m in (1, 2, 4, 8) if m <= world]
+by_n = {}
+for m in sizes:
+    active = rank < m
+    entry = {"raw": raw_block(active, m)}
+    rows = []
+    shapes = [(32, 3)] if quick else [(16, 3), (32, 2), (32, 3), (32, 4), (64, 3), (128, 3)]
+    for chunk_mib, slots in shapes:
+        if active:
+            pkg.check(L.b200v_vector_add_host_config((chunk_mib << 20) // 4, slots))
+        t = job_seconds(pipeline_call, active)
+        rows.append({"chunk_mib": chunk_mib, "slots": slots, "ms": t * 1e3, "e2e_gbs_sum": m * 12 * N / t * 1e-9})
+    entry["pipeline"] = rows
+    best = min(rows, key=lambda r: r["ms"])
+    default = next(r for r in rows if r["chunk_mib"] == 32 and r["slots"] == 3)
+    entry["summary"] = {"n_gpus": m, "e2e_default_gbs": default["e2e_gbs_sum"], "e2e_best_gbs": best["e2e_gbs_sum"],
+                        "best_shape": [best["chunk_mib"], best["slots"]],
+                        "copy_engine_bound_gbs": entry["raw"]["step_mix_e2e_bound_gbs_sum"],
+                        "e2e_default_over_copy_engine_bound": default["e2e_gbs_sum"] / entry["raw"]["step_mix_e2e_bound_gbs_sum"]}
+    by_n[str(m)] = entry
+    if rank == 0:
+        print(f"N={m}", json.dumps(entry["raw"]), flush=True)
+        print(f"N={m}", json.dumps(entry["summary"]), flush=True)
+if rank < world:
+    pkg.check(L.b200v_vector_add_host_config((32 << 20) // 4, 3))
+out["by_n"] = by_n
+
+# ---- every GPU alone, then GPU 0 with each other GPU ---------------------------------------------------
+if world > 1 and not quick:
+    solo = []
+    for k in range(world):
+        t1 = job_seconds(h2d, rank == k, reps=2)
+        t2 = job_seconds(d2h, rank == k, reps=2)
+        solo.append({"gpu": k, "h2d_gbs": GIB / t1 * 1e-9, "d2h_gbs": GIB / t2 * 1e-9})
+    out["solo"] = solo
+    pairs = []
+    for k in range(1, world):
+        t = job_seconds(step_mix, rank in (0, k), reps=2)
+        pairs.append({"gpus": [0, k], "step_mix_ms": t * 1e3, "step_mix_e2e_bound_gbs_sum": 2 * 12 * N / t * 1e-9})
+    out["pairs_with_gpu0"] = pairs
+    if rank == 0:
+        print("solo", json.dumps(solo), flush=True)
+        print("pairs", json.dumps(pairs), flush=True)
+
+# ---- host DRAM as the CPU sees it: all ranks copy / add 1 GiB arrays at once ----------------------------
 import oracle_lib as O  # noqa: E402  (memory-bandwidth probe only)
 OL = O.lib()
 src = np.full(N, 0x3F000000, dtype=np.uint32)
@@ -156,16 +212,14 @@ def host_copy():
     OL.oracle_copy_f32(dst.ctypes.data_as(vp), src.ctypes.data_as(vp), N, threads)
 
 
-t = job_seconds(host_copy)
-host = {"copy_gbs_sum_algorithmic": world * 2 * GIB / t * 1e-9,          # read + write
-        "copy_gbs_sum_with_write_allocate": world * 3 * GIB / t * 1e-9,  # + the read-for-ownership of the destination
-        "threads_per_rank": threads, "ranks": world}
-
-
 def host_add():
     OL.oracle_add_f32(dst.ctypes.data_as(vp), src.ctypes.data_as(vp), hA.view(np.uint32).ctypes.data_as(vp), N, threads)
 
 
+t = job_seconds(host_copy)
+host = {"ranks": world, "threads_per_rank": threads,
+        "copy_gbs_sum_algorithmic": world * 2 * GIB / t * 1e-9,          # read + write
+        "copy_gbs_sum_with_write_allocate": world * 3 * GIB / t * 1e-9}  # + the read-for-ownership of the destination
 t = job_seconds(host_add)
 host["add_gbs_sum_algorithmic"] = world * 3 * GIB / t * 1e-9
 host["add_gbs_sum_with_write_allocate"] = world * 4 * GIB / t * 1e-9
@@ -174,32 +228,58 @@ if rank == 0:
     print("host", json.dumps(host), flush=True)
 del src, dst
 
-# ---- the pipeline itself ---------------------------------------------------------------------------------
-pipeline = []
-chunks = (32,) if quick else (8, 16, 32, 64, 128, 256)
-slot_set = (3,) if quick else (2, 3, 4)
-for chunk_mib in chunks:
-    for slots in slot_set:
-        pkg.check(L.b200v_vector_add_host_config((chunk_mib << 20) // 4, slots))
-        t = job_seconds(lambda: pkg.check(L.b200v_vector_add_host(vp(hA.ptr), vp(hB.ptr), vp(hC.ptr), N)), reps=3)
-        row = {"chunk_mib": chunk_mib, "slots": slots, "ms": t * 1e3, "e2e_gbs_sum": world * 12 * N / t * 1e-9}
-        pipeline.append(row)
-        if rank == 0:
-            print(json.dumps(row), flush=True)
+# ---- the pipeline once more with huge-page-backed, registered host buffers (all ranks) ------------------
+try:
+    maps = []
+    bufs = []
+    for _ in range(3):
+        mm = mmap.mmap(-1, GIB + (2 << 20), flags=mmap.MAP_PRIVATE | mmap.MAP_ANONYMOUS)
+        try:
+            mm.madvise(mmap.MADV_HUGEPAGE)
+        except Exception:
+            pass
+        arr = np.frombuffer(mm, dtype=np.uint8)
+        base = arr.ctypes.data
+        off = (-base) % (2 << 20)
+        view = arr[off:off + GIB].view(np.uint32)
+        view[:] = 0x3F000000                       # touch: pages are faulted in (as huge pages where the kernel agrees)
+        pkg.check(L.b200v_host_register(vp(view.ctypes.data), GIB))
+        maps.append(mm)
+        bufs.append(view)
+
+    class _P:                                      # duck-typed stand-in for PinnedBuffer
+        def __init__(self, v):
+            self.ptr = v.ctypes.data
+
+    pa, pb, pc = (_P(v) for v in bufs)
+    t = job_seconds(lambda: pipeline_call(pa, pb, pc))
+    thp = {"e2e_gbs_sum": world * 12 * N / t * 1e-9, "ms": t * 1e3, "n_gpus": world,
+           "what": "mmap + MADV_HUGEPAGE + b200v_host_register instead of b200v_host_alloc, default pipeline shape"}
+    try:
+        thp["anon_huge_pages_kb"] = int(next(ln for ln in open("/proc/self/smaps_rollup") if ln.startswith("AnonHugePages")).split()[1])
+    except Exception:
+        pass
+    for v in bufs:
+        pkg.check(L.b200v_host_unregister(vp(v.ctypes.data)))
+    out["pipeline_thp_registered"] = thp
+    if rank == 0:
+        print("thp", json.dumps(thp), flush=True)
+except Exception as e:                              # the probe is optional: record why it did not run
+    out["pipeline_thp_registered"] = {"error": repr(e)}
+    if rank == 0:
+        print("thp", repr(e), flush=True)
+
 pkg.check(L.b200v_vector_add_host_release())
-out["pipeline"] = pipeline
-best = min(pipeline, key=lambda r: r["ms"])
-default = next(r for r in pipeline if r["chunk_mib"] == 32 and r["slots"] == 3)
-# the step needs 3 GiB of PCIe traffic per GPU and 3 GiB of host-DRAM traffic per GPU (2 read by the H2D DMA,
-# 1 written by the D2H DMA); its ceiling is whichever of the two the box runs out of first
-pcie_bound = raw["step_mix_e2e_bound_gbs_sum"]
-dram_bound = host["copy_gbs_sum_with_write_allocate"]      # bytes/s the host DRAM has been seen to move
-out["summary"] = {"n_gpus": world, "e2e_default_gbs": default["e2e_gbs_sum"], "e2e_best_gbs": best["e2e_gbs_sum"],
-                  "best_shape": {"chunk_mib": best["chunk_mib"], "slots": best["slots"]},
-                  "copy_engine_bound_gbs": pcie_bound, "host_dram_seen_gbs": dram_bound,
-                  "e2e_over_copy_engine_bound": best["e2e_gbs_sum"] / pcie_bound}
 if rank == 0:
-    print("summary", json.dumps(out["summary"]), flush=True)
+    table = []
+    for m in sizes:
+        s = by_n[str(m)]["summary"]
+        table.append({"n_gpus": m, "e2e_gbs": round(s["e2e_default_gbs"], 1), "e2e_best_shape_gbs": round(s["e2e_best_gbs"], 1),
+                      "copy_engine_bound_gbs": round(s["copy_engine_bound_gbs"], 1),
+                      "host_dram_seen_by_cpu_gbs": round(host["add_gbs_sum_with_write_allocate"], 1),
+                      "e2e_over_bound": round(s["e2e_default_gbs"] / s["copy_engine_bound_gbs"], 3)})
+    out["table"] = table
+    print("table", json.dumps(table), flush=True)
     args = [a for a in sys.argv[1:] if not a.startswith("--")]
     if args:
         json.dump(out, open(args[0], "w"), indent=1)

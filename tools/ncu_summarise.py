@@ -1,0 +1,121 @@
+#!/usr/bin/env python3
+"""Turn Nsight Compute CSV exports into the short tables kept under profiles/.  Developer tool.
+
+  ncu_summarise.py launches <csv from `ncu --metrics gpu__time_duration.sum --csv`> <out.txt> [comment ...]
+      groups the launch list by (kernel, grid): count, average, total, share of the captured GPU time
+  ncu_summarise.py table <csv from `ncu -i rep --page raw --csv`> <out.txt> [comment ...]
+      one row per profiled launch: grid x block, registers, duration, DRAM bytes read / written against
+      the algorithmic bytes, algorithmic TB/s, DRAM throughput % of ncu's peak, achieved occupancy
+  ncu_summarise.py traffic <same raw csv, add kernel only> <out.json> <source text>
+      profiles/traffic.json (what bench.py reports as roofline.traffic)
+"""
+import csv
+import io
+import json
+import re
+import sys
+
+
+def short(name):
+    name = re.sub(r"^void ", "", name)
+    name = re.sub(r"\(.*$", "", name)
+    return name.replace("b200v::", "")
+
+
+def read_long(path):
+    text = "".join(ln for ln in open(path, errors="replace") if ln.startswith('"'))
+    return list(csv.DictReader(io.StringIO(text)))
+
+
+def read_raw(path):
+    text = "".join(ln for ln in open(path, errors="replace") if ln.startswith('"'))
+    rows = list(csv.reader(io.StringIO(text)))
+    head, units, data = rows[0], rows[1], rows[2:]
+    return [dict(zip(head, r)) for r in data], dict(zip(head, units))
+
+
+def num(x):
+    try:
+        return float(str(x).replace(",", ""))
+    except Exception:
+        return float("nan")
+
+
+def algorithmic_bytes(kernel, grid_block_bytes):
+    """bytes the launch is asked to move at 1 GiB per array (tools/profile_all.py)"""
+    gib = float(1 << 30)
+    m = re.match(r"stream_kernel<(\d)", kernel)
+    if m:
+        return (3 if m.group(1) in "03" else 2) * gib
+    if kernel.startswith(("fill_kernel", "checksum_kernel")):
+        return gib
+    return float("nan")
+
+
+def cmd_launches(src, dst, comment):
+    rows = [r for r in read_long(src) if r.get("Metric Name") == "gpu__time_duration.sum"]
+    groups, order = {}, []
+    for r in rows:
+        key = (short(r["Kernel Name"]), r["Grid Size"], r["Block Size"])
+        if key not in groups:
+            groups[key] = []
+            order.append(key)
+        groups[key].append(num(r["Metric Value"]) / 1e3)
+    total = sum(sum(v) for v in groups.values())
+    with open(dst, "w") as f:
+        for c in comment:
+            f.write(f"# {c}\n")
+        f.write("# grouped by (kernel, grid): count, avg us, total us, share of all captured GPU time\n")
+        for key in order:
+            v = groups[key]
+            f.write(f"{len(v):5d} x {sum(v) / len(v):9.1f} us = {sum(v):12.1f} us  {100 * sum(v) / total:5.1f}%  {key[0]}  grid={key[1]} block={key[2]}\n")
+        f.write(f"# total {total:.1f} us over {len(rows)} launches\n")
+    print(open(dst).read())
+
+
+def cmd_table(src, dst, comment):
+    rows, _ = read_raw(src)
+    with open(dst, "w") as f:
+        for c in comment:
+            f.write(f"# {c}\n")
+        f.write("# columns: kernel | grid x block | regs | duration us | DRAM read GB | DRAM write GB | algorithmic GB | traffic/algorithmic | "
+                "TB/s (algorithmic / duration) | DRAM throughput % of ncu peak | achieved occupancy % | L2 hit %\n")
+        for r in rows:
+            k = short(r["Kernel Name"])
+            dur = num(r.get("gpu__time_duration.sum")) / 1e3
+            rd, wr = num(r.get("dram__bytes_read.sum")), num(r.get("dram__bytes_write.sum"))
+            alg = algorithmic_bytes(k, None)
+            thr = num(r.get("gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", r.get("dram__throughput.avg.pct_of_peak_sustained_elapsed")))
+            occ = num(r.get("sm__warps_active.avg.pct_of_peak_sustained_active"))
+            l2 = num(r.get("lts__t_sector_hit_rate.pct"))
+            regs = r.get("launch__registers_per_thread", "")
+            f.write(f"{k:<48} | {r['Grid Size']:>15} x {r['Block Size']:>13} | {regs:>3} | {dur:8.1f} | {rd / 1e9:6.3f} | {wr / 1e9:6.3f} | "
+                    f"{alg / 1e9:6.3f} | {(rd + wr) / alg:5.3f} | {alg / dur / 1e6:7.2f} | {thr:5.1f} | {occ:5.1f} | {l2:5.1f}\n")
+        f.write("# stream_kernel<OP, BF16, VECB, UNROLL, BLOCK, LD, ST, PDL>: OP 0 add, 1 copy, 2 scale, 3 triad; fill_kernel<BF16, MODE>\n")
+        f.write("# (durations under ncu are single cold launches; the timed numbers are in the bench and sweep files)\n")
+    print(open(dst).read())
+
+
+def cmd_traffic(src, dst, source_text):
+    rows, _ = read_raw(src)
+    rows = [r for r in rows if "stream_kernel<0, false, 32" in r["Kernel Name"] or "stream_kernel<0, 0, 32" in r["Kernel Name"]]
+    rd = [num(r["dram__bytes_read.sum"]) for r in rows]
+    wr = [num(r["dram__bytes_write.sum"]) for r in rows]
+    alg = 12 * (1 << 28)
+    per = (sum(rd) + sum(wr)) / len(rows)
+    out = {"add_f32_2p28": {
+        "dram_bytes_per_launch": int(round(per)), "dram_bytes_read": int(round(sum(rd) / len(rows))),
+        "dram_bytes_write": int(round(sum(wr) / len(rows))), "algorithmic_bytes": alg, "ratio_to_algorithmic": round(per / alg, 4),
+        "gpu_time_ns_under_ncu": [int(num(r["gpu__time_duration.sum"])) for r in rows],
+        "dram_throughput_pct_of_ncu_peak": [num(r.get("gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "nan")) for r in rows],
+        "l2_hit_rate_pct": [num(r.get("lts__t_sector_hit_rate.pct", "nan")) for r in rows],
+        "kernel": short(rows[0]["Kernel Name"]), "grid": rows[0]["Grid Size"], "block": rows[0]["Block Size"],
+        "source": source_text,
+        "note": "writes are ~3 % under the algorithmic 1 GiB because the last ~34 MB of output is still dirty in the 126 MB L2 when the kernel ends; reads equal the algorithmic 2 GiB"}}
+    json.dump(out, open(dst, "w"), indent=1)
+    print(json.dumps(out, indent=1))
+
+
+if __name__ == "__main__":
+    mode, src, dst, rest = sys.argv[1], sys.argv[2], sys.argv[3], sys.argv[4:]
+    {"launches": cmd_launches, "table": cmd_table}.get(mode, lambda s, d, r: cmd_traffic(s, d, " ".join(r)))(src, dst, rest)
