@@ -12,8 +12,8 @@ B="python bench.py --steps 20 --warmup 5 --no-cpu --no-native --no-sharded --e2e
 $B > $O/r02_bench_for_ncu.json 2>&1; echo "bench (ncu shape) rc=$?"
 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $O/r02_ncu_launches_raw.csv $B > $O/r02_ncu_launches.log 2>&1; echo "ncu launches rc=$?"
 ncu --set full --clock-control none --import-source on -k regex:stream_kernel -s 8 -c 3 -f -o $O/r02_add_full $B > $O/r02_ncu_add_full.log 2>&1; echo "ncu add full rc=$?"
-ncu -i $O/r02_add_full.ncu-rep --page raw --csv > $O/r02_ncu_add_full_raw.csv 2>/dev/null
+ncu -i $O/r02_add_full.ncu-rep --page raw --csv --print-units base > $O/r02_ncu_add_full_raw.csv 2>/dev/null
 ncu --set full --clock-control none -k regex:'stream_kernel|checksum_kernel|fill_kernel' -s 13 -c 13 -f -o $O/r02_all_kernels python tools/profile_all.py > $O/r02_ncu_all.log 2>&1; echo "ncu all rc=$?"
-ncu -i $O/r02_all_kernels.ncu-rep --page raw --csv > $O/r02_ncu_all_kernels_raw.csv 2>/dev/null
+ncu -i $O/r02_all_kernels.ncu-rep --page raw --csv --print-units base > $O/r02_ncu_all_kernels_raw.csv 2>/dev/null
 python tools/e2e_scaling.py $O/r02_e2e_scaling_1gpubox.json 2>&1 | tail -12
 ls -la $O | tail -20
