@@ -11,7 +11,7 @@ python -m torch.distributed.run --nnodes=1 --nproc-per-node $G --master-addr 127
 ./kubernetes-with-nvidia-gpu_b200/gpu-validate --mode full --seconds 10 --hbm-fraction 0.9 --fail-on-throttle --json $O/r02_full_${G}gpu.json > $O/r02_full_${G}gpu_job_command.log 2>&1; echo "full rc=$?"; tail -14 $O/r02_full_${G}gpu_job_command.log
 python - <<PY
 import json
-d = json.load(open("$O/r02_bench_n${G}.json"))
+d = json.loads([l for l in open("$O/r02_bench_n${G}.json") if l.startswith("{")][-1])
 print({k: d[k] for k in ("value", "n_gpus")}, d["e2e"]["value"], d["parity"], d["triad_sharded_2p32"]["node_gbs"], d["triad_sharded_2p32"]["matches_oracle"],
       d["native_node"]["node_gbs"], d["native_node"]["ok"], d["p2p"]["ok"], d["p2p"]["gbs"], d["sustained"]["add"]["gbs"], d["sustained"]["add"]["clocks"])
 PY
