@@ -25,10 +25,14 @@ Further keys, all measured in the same run:
                         compared with the oracle's;
   `parity`              at every N: each rank's whole 2^28-element output against the oracle's loop over
                         the same global indices (checksum), AND over ranks; the run fails if false;
-  `native_node`, `p2p`  rank 0, after every rank has freed its buffers: the pod entrypoint's own
-                        per-GPU shard launcher (`gpu-validate --mode node`, fork/exec + pipe barrier) on
-                        the same 2^32-element triad, and the all-pairs NVLink check (`--mode p2p`,
-                        BASELINE.json configs[4]) — the product binaries, run as subprocesses.
+  `native_node`         rank 0, after every rank has freed its buffers: the pod entrypoint's own per-GPU shard
+                        launcher (`gpu-validate --mode node`, fork/exec + pipe barrier) on the same 2^32-element
+                        triad;
+  `burnin`, `p2p`       rank 0: BASELINE.json configs[4] through the Job manifest's own command (`gpu-validate
+                        --mode full --hbm-fraction F --fail-on-throttle`, with a shorter burn-in): per-GPU triad
+                        burn-in over a share of every GPU's HBM with every pass verified, then all ordered GPU
+                        pairs over NVLink by copy engine, peer loads and peer stores (`p2p` is null at N = 1).
+                        These legs run the product binaries as subprocesses.
 The oracle is only ever executed as the checker (parity legs) or as the timed CPU baseline
 (`cpu_baseline`, `--impl reference`), never on the GPU arm's product path.
 `--impl reference` times the CPU loop as the reference arm: the reference repo itself has no
@@ -284,10 +288,10 @@ def run_reference(args, rank):
 # ------------------------------------------------------------------------------------------------
 # rank 0: the product's own binaries as subprocesses (native shard launcher, NVLink check)
 
-def run_native(pkg, mode_args, json_name, timeout):
+def run_native(pkg, mode_args, json_name, timeout, json_path=None):
     """Runs gpu-validate with --json; returns a dict: rc, verdict line, parsed json (or None), summary lines."""
     with tempfile.TemporaryDirectory() as td:
-        js = os.path.join(td, json_name)
+        js = json_path or os.path.join(td, json_name)
         cmd = [pkg.LAUNCHER_PATH, *mode_args, "--json", js]
         env = dict(os.environ, OMP_NUM_THREADS=str(host_cores()))     # torchrun exports OMP_NUM_THREADS=1
         t0 = time.perf_counter()
@@ -326,16 +330,43 @@ def native_node_leg(pkg, world, iters):
     return out
 
 
-def native_p2p_leg(pkg, world, p2p_bytes):
-    r = run_native(pkg, ["--mode", "p2p", "--gpus", str(world), "--p2p-bytes", str(p2p_bytes), "--iters", "12"], "p2p.json", 600)
+def native_full_leg(pkg, world, p2p_bytes, seconds, hbm_fraction):
+    """The Job manifest's command (deploy/job-node-validate.yaml: burn-in over a share of every GPU's HBM with every
+    pass verified and thermal / hardware slowdown failing the run, then the all-pairs NVLink check) with a shorter
+    burn-in; returns (burnin, p2p) — the two halves of BASELINE.json configs[4]."""
+    args = ["--mode", "full", "--gpus", str(world), "--seconds", f"{seconds:g}", "--hbm-fraction", f"{hbm_fraction:g}",
+            "--fail-on-throttle", "--p2p-bytes", str(p2p_bytes), "--iters", "12"]
+    with tempfile.TemporaryDirectory() as td:
+        js = os.path.join(td, "full.json")
+        r = run_native(pkg, args, "full.json", 800, json_path=js)
+        try:
+            with open(js + ".p2p") as f:
+                pj = json.load(f)
+        except Exception:
+            pj = None
     d = r.pop("json")
-    out = dict(r, what="all ordered GPU pairs over NVLink (BASELINE.json configs[4]): cudaMemcpyPeer, a kernel loading from the peer, a kernel "
-                       "storing into the peer; then every GPU sending and receiving at once; every transfer verified by checksum on the destination")
+    common = {k: r[k] for k in ("cmd", "rc", "verdict", "wall_s")}
+    burn = dict(common, summary_lines=[ln for ln in r["summary_lines"] if not ln.startswith("[p2p]")],
+                what="per-GPU triad burn-in, one process per GPU, arrays sized to a share of each GPU's free HBM, EVERY pass verified against "
+                     "the host loop's checksum, NVML clocks / temperature / power / ECC read under load (BASELINE.json configs[4], first half)")
     if d:
-        out.update({"gpus": d["gpus"], "bytes_per_transfer": d["bytes"], "pairs": len(d["pairs"]), "verified": bool(d["ok"]),
-                    "nvlink_gbs_per_direction": d.get("nvlink_gbs_per_direction", NVLINK_GBS), "gbs": d.get("summary")})
-    out["ok"] = out["rc"] == 0 and out["verdict"] == "Test PASSED" and bool(d) and out.get("verified", False)
-    return out
+        burn.update({"gpus": d["gpus"], "elements_per_gpu": d["ranks"][0]["elements"], "hbm_fraction": hbm_fraction,
+                     "passes_per_gpu": [k["passes"] for k in d["ranks"]], "node_gbs": d["node_gbs"], "gbs_per_gpu": round(d["node_gbs"] / d["gpus"], 1),
+                     "frac_of_nominal_8000_per_gpu": round(d["node_gbs"] / d["gpus"] / NOMINAL_GBS, 4),
+                     "verified": bool(d["ok"]) and all(k["ok"] == 1 for k in d["ranks"]),
+                     "under_load": [{"rank": k["rank"], "sm_min_mhz": k["sm_min_mhz"], "temp_max_c": k["temp_max_c"], "power_max_w": k["power_max_w"],
+                                     "clock_limit_reasons": k["clock_limit_reasons"]} for k in d["ranks"]]})
+    burn["ok"] = r["rc"] == 0 and r["verdict"] == "Test PASSED" and bool(d) and burn.get("verified", False)
+    if world < 2:
+        return burn, None
+    p2p = dict(common, summary_lines=[ln for ln in r["summary_lines"] if ln.startswith("[p2p]")],
+               what="all ordered GPU pairs over NVLink (BASELINE.json configs[4], second half): cudaMemcpyPeer, a kernel loading from the peer, a kernel "
+                    "storing into the peer; then every GPU sending and receiving at once; every transfer verified by checksum on the destination")
+    if pj:
+        p2p.update({"gpus": pj["gpus"], "bytes_per_transfer": pj["bytes"], "pairs": len(pj["pairs"]), "verified": bool(pj["ok"]),
+                    "nvlink_gbs_per_direction": pj.get("nvlink_gbs_per_direction", NVLINK_GBS), "gbs": pj.get("summary")})
+    p2p["ok"] = r["rc"] == 0 and r["verdict"] == "Test PASSED" and bool(pj) and p2p.get("verified", False)
+    return burn, p2p
 
 
 # ------------------------------------------------------------------------------------------------
@@ -351,6 +382,8 @@ def main():
     ap.add_argument("--no-sharded", action="store_true", help="skip the 2^32-element sharded triad leg")
     ap.add_argument("--no-native", action="store_true", help="skip the gpu-validate subprocess legs (native_node, p2p)")
     ap.add_argument("--p2p-bytes", type=int, default=1 << 30)
+    ap.add_argument("--burnin-seconds", type=float, default=4.0, help="length of the burn-in inside the gpu-validate --mode full leg")
+    ap.add_argument("--hbm-fraction", type=float, default=0.5, help="share of each GPU's free HBM the burn-in arrays cover")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
 
@@ -553,11 +586,10 @@ def main():
     R.barrier()
 
     # ---- rank 0 alone: the product's own launcher binaries; the other ranks wait on the host (no GPU work) ----
-    native_node = p2p = None
+    native_node = burnin = p2p = None
     if rank == 0 and not args.no_native and os.path.exists(pkg.LAUNCHER_PATH):
         native_node = native_node_leg(pkg, world, iters=20)
-        if world > 1:
-            p2p = native_p2p_leg(pkg, world, args.p2p_bytes)
+        burnin, p2p = native_full_leg(pkg, world, args.p2p_bytes, args.burnin_seconds, args.hbm_fraction)
     R.host_barrier()
     if rank != 0:
         R.close()
@@ -592,7 +624,7 @@ def main():
         "parity": {"job_checksum": hex_pair(job_checksum),
                    "e2e_matches_device": e2e_ok, "e2e_check": "host result checksum == device-resident result checksum, every rank",
                    "device_matches_cpu_baseline": parity_ok, "how": parity_how},
-        "native_node": native_node, "p2p": p2p,
+        "native_node": native_node, "burnin": burnin, "p2p": p2p,
         "clocks": sampler.summary(),
     }
     if not args.no_cpu and world == 1:      # the timed CPU baseline is reported on rank 0 at N = 1 only
@@ -605,7 +637,7 @@ def main():
     print(json.dumps(line), flush=True)
     R.close()
     ok = (parity_ok is not False) and e2e_ok and sharded_ok
-    ok = ok and (native_node is None or native_node["ok"]) and (p2p is None or p2p["ok"])
+    ok = ok and all(leg is None or leg["ok"] for leg in (native_node, burnin, p2p))
     return 0 if ok else 1
 
 

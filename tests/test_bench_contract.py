@@ -63,7 +63,7 @@ def test_oracle_shard_checksums_add_up():
 
 @pytest.mark.gpu
 def test_our_arm_line():
-    d = run_bench("--steps", "30", "--warmup", "3", "--e2e-steps", "2", "--sustained-seconds", "0.5", timeout=900)
+    d = run_bench("--steps", "30", "--warmup", "3", "--e2e-steps", "2", "--sustained-seconds", "0.5", "--burnin-seconds", "1.5", timeout=900)
     assert BASE_KEYS <= set(d) and "impl" not in d
     assert d["metric"].startswith("vectorAdd/triad HBM GB/s") and d["scaling"] == "weak" and d["data"] == "synthetic"
     assert d["n_gpus"] == 1 and d["steps"] == 30 and d["gpu_launches"] == 30
@@ -96,4 +96,9 @@ def test_our_arm_line():
     nn = d["native_node"]
     assert nn["ok"] and nn["verified"] and nn["verdict"] == "Test PASSED" and nn["elements"] == 1 << 32 and nn["gpus"] == 1
     assert nn["node_gbs_from"] == "max over ranks of mean ms" and 3000 < nn["node_gbs"] < 12000
+    # the Job manifest's command (burn-in over a share of the HBM, every pass verified; then the NVLink check)
+    bi = d["burnin"]
+    assert bi["ok"] and bi["verified"] and bi["verdict"] == "Test PASSED" and "--mode full" in bi["cmd"] and "--fail-on-throttle" in bi["cmd"]
+    assert bi["elements_per_gpu"] > (1 << 32) and min(bi["passes_per_gpu"]) >= 2 and 3000 < bi["gbs_per_gpu"] < 12000
+    assert bi["under_load"][0]["power_max_w"] > 200
     assert d["p2p"] is None          # one GPU: no pair to check

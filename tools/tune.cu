@@ -433,6 +433,9 @@ int main(int argc, char** argv)
         add_shapes<OP_COPY, LD_NC_NA, ST_DEFAULT>("shape");
         add_shapes<OP_COPY, LD_DEFAULT, ST_DEFAULT>("shape");
     }
+    if (!strcmp(stage, "persist")) {   // the shipped add shape alone, grid = tiles and 1/2/4 CTAs per SM: for an ncu side-by-side
+        add_cfg<OP_ADD, 32, 4, 512, LD_DEFAULT, ST_DEFAULT>("persist");
+    }
     if (!strcmp(stage, "scale")) {
         add_shapes<OP_SCALE, LD_NC_NA, ST_DEFAULT>("scale");
         add_shapes<OP_SCALE, LD_DEFAULT, ST_DEFAULT>("scale");
