@@ -113,6 +113,60 @@ persistent_probe_kernel(void* __restrict__ dst, const void* __restrict__ x, cons
     }
 }
 
+// Mechanism probes for "why does a persistent grid lose to one tile per CTA?" (profiles/r02_persist_vs_tiles.txt).
+//   MODE 0: plain persistent loop (as persistent_probe_kernel)
+//   MODE 1: the same with __syncthreads() at the top of every tile: the CTA's 16 warps stay in phase, so every tile is
+//           requested as one 2 x 64 KiB burst, as it is when a fresh CTA starts (tests: request-phase coherence)
+//   MODE 2: persistent CTAs that FETCH their next tile from a global counter instead of owning a fixed stride (tests:
+//           dynamic load balancing over SMs); the fetch needs a CTA-wide broadcast, so it implies MODE 1's barrier
+//   MODE 3: static stride, but the CTA's whole tile range is contiguous (CTA b owns tiles [b*T/G, (b+1)*T/G)) — each SM
+//           streams its own private region (tests: does it matter that concurrently active tiles are neighbours?)
+__device__ unsigned long long g_tile_counter;
+
+template <int OP, int UNROLL, int BLOCK, int MODE>
+__global__ void __launch_bounds__(BLOCK)
+mechanism_probe_kernel(void* __restrict__ dst, const void* __restrict__ x, const void* __restrict__ y, float s, size_t n)
+{
+    using V = Vec<32>;
+    constexpr size_t TILE_VECS = (size_t)BLOCK * UNROLL;
+    const size_t full_tiles = n / (TILE_VECS * 8);
+    V* vd = reinterpret_cast<V*>(dst);
+    const V* vx = reinterpret_cast<const V*>(x);
+    const V* vy = reinterpret_cast<const V*>(y);
+    __shared__ unsigned long long next_tile;
+    size_t tile = blockIdx.x, end = full_tiles, step = gridDim.x;
+    if (MODE == 3) {
+        tile = full_tiles * blockIdx.x / gridDim.x;
+        end = full_tiles * (blockIdx.x + 1) / gridDim.x;
+        step = 1;
+    }
+    while (true) {
+        if (MODE == 2) {
+            __syncthreads();
+            if (threadIdx.x == 0) next_tile = atomicAdd(&g_tile_counter, 1ull);
+            __syncthreads();
+            tile = next_tile;
+        } else if (MODE == 1) {
+            __syncthreads();
+        }
+        if (tile >= end) break;
+        const size_t base = tile * TILE_VECS + threadIdx.x;
+        V a[UNROLL], b[UNROLL];
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) a[u] = ldg<LD_DEFAULT>(vx + base + (size_t)u * BLOCK);
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) b[u] = ldg<LD_DEFAULT>(vy + base + (size_t)u * BLOCK);
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) {
+            V r;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) r.w[k] = op_word<OP, false>(a[u].w[k], b[u].w[k], s);
+            stg<ST_DEFAULT>(vd + base + (size_t)u * BLOCK, r);
+        }
+        tile += step;
+    }
+}
+
 struct Config {
     std::string stage;
     int op, vecb, unroll, block, ldh, sth;
@@ -173,6 +227,26 @@ template <int OP, int UNROLL, int BLOCK, bool STAGGER> static void add_probe(con
     CK(cudaFuncGetAttributes(&fa, k));
     c.regs = fa.numRegs;
     c.launch = [k](unsigned grid, void* d, const void* x, const void* y, float s, size_t n) { k<<<grid, BLOCK>>>(d, x, y, s, n); };
+    g_cfg.push_back(c);
+}
+
+template <int OP, int UNROLL, int BLOCK, int MODE> static void add_mechanism(const char* stage)
+{
+    Config c;
+    c.stage = stage;
+    c.op = OP; c.vecb = 32; c.unroll = UNROLL; c.block = BLOCK; c.ldh = 10 + MODE; c.sth = 0;   // ld 10..13 = mechanism probe MODE 0..3
+    c.tile_elems = (size_t)BLOCK * UNROLL * 8;
+    auto k = mechanism_probe_kernel<OP, UNROLL, BLOCK, MODE>;
+    cudaFuncAttributes fa;
+    CK(cudaFuncGetAttributes(&fa, k));
+    c.regs = fa.numRegs;
+    c.launch = [k](unsigned grid, void* d, const void* x, const void* y, float s, size_t n) {
+        if (MODE == 2) {
+            unsigned long long zero = 0;
+            CK(cudaMemcpyToSymbolAsync(g_tile_counter, &zero, sizeof zero, 0, cudaMemcpyHostToDevice, 0));
+        }
+        k<<<grid, BLOCK>>>(d, x, y, s, n);
+    };
     g_cfg.push_back(c);
 }
 
@@ -435,6 +509,18 @@ int main(int argc, char** argv)
     }
     if (!strcmp(stage, "persist")) {   // the shipped add shape alone, grid = tiles and 1/2/4 CTAs per SM: for an ncu side-by-side
         add_cfg<OP_ADD, 32, 4, 512, LD_DEFAULT, ST_DEFAULT>("persist");
+    }
+    if (!strcmp(stage, "mechanism")) {   // ld column: 0 = product kernel, 10 = plain persistent, 11 = + CTA barrier per tile, 12 = dynamic tile fetch, 13 = contiguous range per CTA
+        add_cfg<OP_ADD, 32, 4, 512, LD_DEFAULT, ST_DEFAULT>("mechanism");
+        add_mechanism<OP_ADD, 4, 512, 0>("mechanism");
+        add_mechanism<OP_ADD, 4, 512, 1>("mechanism");
+        add_mechanism<OP_ADD, 4, 512, 2>("mechanism");
+        add_mechanism<OP_ADD, 4, 512, 3>("mechanism");
+        add_cfg<OP_ADD, 32, 1, 256, LD_DEFAULT, ST_DEFAULT>("mechanism");
+        add_mechanism<OP_ADD, 1, 256, 0>("mechanism");
+        add_mechanism<OP_ADD, 1, 256, 1>("mechanism");
+        add_mechanism<OP_ADD, 1, 256, 2>("mechanism");
+        add_mechanism<OP_ADD, 1, 256, 3>("mechanism");
     }
     if (!strcmp(stage, "scale")) {
         add_shapes<OP_SCALE, LD_NC_NA, ST_DEFAULT>("scale");
