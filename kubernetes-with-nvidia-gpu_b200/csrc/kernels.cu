@@ -154,33 +154,60 @@ __device__ __forceinline__ uint32_t gen_bf16_bits(uint32_t key, uint64_t index, 
     return b;
 }
 
-// The fill is integer-ALU bound (ncu: ALU pipe 95 %, DRAM 48 % for the first version).  The vector
-// body therefore takes the generator mode as a template parameter and hoists the high-half term of
-// the hash out of the per-element work (32-bit index arithmetic; a vector that straddles a 2^32 index
-// boundary takes the plain path): 4.2 -> 5.9 TB/s for fp32, 3.6 -> 4.3 TB/s for bf16.  Doing the
-// shifts as multiply-high on the FMA pipe was tried and is slower (IMAD.HI is half rate).
+// The fill is integer-ALU bound (ncu: ALU pipe 94 %, DRAM 70 % for fp32 — profiles/r02_ncu_all_kernels.txt), so the
+// vector body spends as few ALU-pipe instructions per element as the integer spec allows:
+//  * the generator mode is a template parameter;
+//  * the hash's high-half term is hoisted out of the per-element work (32-bit index arithmetic; a vector that
+//    straddles a 2^32 index boundary takes the plain path);
+//  * when the first index of every vector is a multiple of the vector length (ALIGNED; true whenever start + head is,
+//    which the host checks once), lo + k == lo ^ k, so (lo + k) ^ kh is ONE xor with a hoisted lo ^ kh;
+//  * the last xor-shift of mix32 is folded into what consumes it: for fp32 UNIT, (float)(h >> 8) * 2^-24 is computed
+//    as (float)(h & 0xFFFFFF00) * 2^-32 (same value: 24 significant bits either way), and (x ^ t) & mask is a single
+//    LOP3; bf16 only ever reads the top 16 bits of h, which the last xor-shift (x ^= x >> 16) does not change, so it
+//    is skipped there.
+// First version 4.2 / 3.6 TB/s (fp32 / bf16 UNIT), round 1 5.9 / 4.3, now 6.9 / 6.1 (cudaMemset: 7.1).  Doing the shifts as
+// multiply-high on the FMA pipe was tried and is slower (IMAD.HI is half rate).
 // Same integer function as mix32/hash32 above, bit for bit (tests/test_gpu_parity.py: fill vs oracle).
 
-template <int MODE> __device__ __forceinline__ uint32_t f32_from_hash(uint32_t h)
+// mix32 up to and including the second multiply; h = x ^ (x >> 16) is left to the consumer
+__device__ __forceinline__ uint32_t mix32_head(uint32_t x)
 {
-    if constexpr (MODE == B200V_GEN_UNIT) return __float_as_uint(__fmul_rn((float)(h >> 8), 0x1p-24f));
-    else if constexpr (MODE == B200V_GEN_DENORM) return h & 0x81FFFFFFu;
-    else return (h & 0x7F800000u) == 0x7F800000u ? h & ~0x00800000u : h;
+    x ^= x >> 16;
+    x *= 0x7FEB352Du;
+    x ^= x >> 15;
+    x *= 0x846CA68Bu;
+    return x;
 }
 
-template <int MODE> __device__ __forceinline__ uint32_t bf16_from_hash(uint32_t h)
+template <int MODE> __device__ __forceinline__ uint32_t f32_from_head(uint32_t x)
 {
-    if constexpr (MODE == B200V_GEN_UNIT) return __float_as_uint(__fmul_rn((float)(h >> 24), 0x1p-8f)) >> 16;
-    else if constexpr (MODE == B200V_GEN_DENORM) return (h >> 16) & 0x81FFu;
-    else {
-        const uint32_t b = h >> 16;
-        return (b & 0x7F80u) == 0x7F80u ? b & ~0x0080u : b;
+    const uint32_t t = x >> 16;
+    if constexpr (MODE == B200V_GEN_UNIT) {
+        return __float_as_uint(__fmul_rn((float)((x ^ t) & 0xFFFFFF00u), 0x1p-32f));
+    } else if constexpr (MODE == B200V_GEN_DENORM) {
+        return (x ^ t) & 0x81FFFFFFu;
+    } else {
+        const uint32_t h = x ^ t;
+        return (~h & 0x7F800000u) == 0u ? h & ~0x00800000u : h;
+    }
+}
+
+template <int MODE> __device__ __forceinline__ uint32_t bf16_from_head(uint32_t x)
+{
+    // h >> 16 == x >> 16: the last xor-shift only touches the low half
+    if constexpr (MODE == B200V_GEN_UNIT) {
+        return __float_as_uint(__fmul_rn((float)(x >> 24), 0x1p-8f)) >> 16;
+    } else if constexpr (MODE == B200V_GEN_DENORM) {
+        return (x >> 16) & 0x81FFu;
+    } else {
+        const uint32_t b = x >> 16;
+        return (~b & 0x7F80u) == 0u ? b & ~0x0080u : b;
     }
 }
 
 // One thread produces 16 bytes (4 fp32 / 8 bf16) where dst is 16-byte aligned; the ragged
 // head and tail are written element-wise.
-template <bool BF16, int MODE>
+template <bool BF16, int MODE, bool ALIGNED>
 __global__ void __launch_bounds__(256)
 fill_kernel(void* __restrict__ dst, uint64_t start, size_t n, uint32_t key)
 {
@@ -196,13 +223,15 @@ fill_kernel(void* __restrict__ dst, uint64_t start, size_t n, uint32_t key)
         const uint64_t i0 = start + head + v * EPV;
         const uint32_t lo0 = (uint32_t)i0;
         uint32_t w[EPV];
-        if (lo0 <= 0xFFFFFFFFu - (uint32_t)EPV) {
+        if (ALIGNED || lo0 <= 0xFFFFFFFFu - (uint32_t)EPV) {
             // all EPV indices share the high half: one hoisted term, 32-bit index arithmetic
+            // (ALIGNED: lo0 is a multiple of EPV, so the vector can never straddle a 2^32 boundary)
             const uint32_t kh = key ^ ((uint32_t)(i0 >> 32) * 0x9E3779B9u);
+            const uint32_t base = lo0 ^ kh;
 #pragma unroll
             for (int k = 0; k < (int)EPV; ++k) {
-                const uint32_t h = mix32((lo0 + (uint32_t)k) ^ kh);
-                w[k] = BF16 ? bf16_from_hash<MODE>(h) : f32_from_hash<MODE>(h);
+                const uint32_t x = mix32_head(ALIGNED ? base ^ (uint32_t)k : (lo0 + (uint32_t)k) ^ kh);
+                w[k] = BF16 ? bf16_from_head<MODE>(x) : f32_from_head<MODE>(x);
             }
         } else {
 #pragma unroll
@@ -379,25 +408,39 @@ int b200v_fill(int dtype, void* d_dst, uint64_t start, size_t n, uint32_t seed, 
     const uint32_t key = mix32(seed ^ (0x9E3779B9u * (stream_id + 1u)));
     const size_t epv = dtype == B200V_BF16 ? 8 : 4;
     size_t grid = (n / epv + 255) / 256 + 1;
-    const size_t cap = (size_t)sms * 16;
+    // 64 CTAs per SM (8 waves of 8 resident CTAs): enough CTAs for the block scheduler to even out the SMs, few enough
+    // that their prologues do not show.  1 GiB fp32 UNIT: 16/SM 6.40, 32/SM 6.73, 64/SM 6.93, 128/SM 7.05 (but bf16 and
+    // BITS drop), 256/SM 6.40, one vector per thread (262144 CTAs) 2.8 TB/s (profiles/r02_time_fill.txt).
+    const size_t cap = (size_t)sms * 64;
     if (grid > cap) grid = cap;
     cudaStream_t st = as_stream(stream);
     const unsigned g = (unsigned)grid;
     const bool bf = dtype == B200V_BF16;
+    // is the first index of every vector a multiple of the vector length?  (head = the kernel's: elements before
+    // 16-byte alignment of the destination)
+    size_t head = ((16 - ((uintptr_t)d_dst & 15)) & 15) / esz;
+    if (head > n) head = n;
+    const bool aligned = ((start + head) % epv) == 0;
+#define B200V_FILL(BF, MODE)                                                                  \
+    do {                                                                                      \
+        if (aligned) fill_kernel<BF, MODE, true><<<g, 256, 0, st>>>(d_dst, start, n, key);    \
+        else fill_kernel<BF, MODE, false><<<g, 256, 0, st>>>(d_dst, start, n, key);           \
+    } while (0)
     switch (mode) {
     case B200V_GEN_UNIT:
-        if (bf) fill_kernel<true, B200V_GEN_UNIT><<<g, 256, 0, st>>>(d_dst, start, n, key);
-        else fill_kernel<false, B200V_GEN_UNIT><<<g, 256, 0, st>>>(d_dst, start, n, key);
+        if (bf) B200V_FILL(true, B200V_GEN_UNIT);
+        else B200V_FILL(false, B200V_GEN_UNIT);
         break;
     case B200V_GEN_BITS:
-        if (bf) fill_kernel<true, B200V_GEN_BITS><<<g, 256, 0, st>>>(d_dst, start, n, key);
-        else fill_kernel<false, B200V_GEN_BITS><<<g, 256, 0, st>>>(d_dst, start, n, key);
+        if (bf) B200V_FILL(true, B200V_GEN_BITS);
+        else B200V_FILL(false, B200V_GEN_BITS);
         break;
     default:
-        if (bf) fill_kernel<true, B200V_GEN_DENORM><<<g, 256, 0, st>>>(d_dst, start, n, key);
-        else fill_kernel<false, B200V_GEN_DENORM><<<g, 256, 0, st>>>(d_dst, start, n, key);
+        if (bf) B200V_FILL(true, B200V_GEN_DENORM);
+        else B200V_FILL(false, B200V_GEN_DENORM);
         break;
     }
+#undef B200V_FILL
     B200V_CUDA(cudaGetLastError());
     return B200V_OK;
 }

@@ -79,8 +79,14 @@ def test_discovery(L):
 @pytest.mark.parametrize("mode", [O.GEN_UNIT, O.GEN_BITS, O.GEN_DENORM])
 def test_fill_matches_oracle(L, dtype, mode):
     e = esz(dtype)
+    # (start, n, element offset of the destination): both vector paths of the kernel — first index of every vector a
+    # multiple of the vector length (start + head aligned: the hoisted-xor path) or not — across the 2^32 index boundary,
+    # with ragged heads and tails
     for start, n, off in ((0, 1, 0), (0, 50_000, 0), (5, 100_003, 0), ((1 << 32) - 777, 4099, 0),
-                          ((1 << 34) + 1, 1 << 20, 0), (9, 1237, 1), (9, 1237, 3), (0, 7, 5)):
+                          ((1 << 34) + 1, 1 << 20, 0), (9, 1237, 1), (9, 1237, 3), (0, 7, 5),
+                          ((1 << 32) - 4096, 8192 + 3, 0), ((1 << 32) - 8, 64, 0), ((1 << 33) + 16, 100_001, 0),
+                          (7, 40_001, 1), (3, 40_001, 5), ((1 << 32) - 1029, 4099, 5), (8, (1 << 20) + 9, 0),
+                          (1, 40_001, 1), ((1 << 32) - 1027, 4099, 5), ((1 << 32) - 1031, 4099, 1)):
         buf = pkg.DeviceBuffer(n * e + off * e + 64)
         pkg.check(L.b200v_memset(C.c_void_p(buf.ptr), 0x5A, buf.nbytes, None))
         pkg.check(L.b200v_fill(pkg.DTYPES[dtype], buf.at(off * e), start, n, SEED, 3, mode, None))

@@ -91,7 +91,7 @@ def cmd_table(src, dst, comment):
             regs = r.get("launch__registers_per_thread", "")
             f.write(f"{k:<48} | {r['Grid Size']:>15} x {r['Block Size']:>13} | {regs:>3} | {dur:8.1f} | {rd / 1e9:6.3f} | {wr / 1e9:6.3f} | "
                     f"{alg / 1e9:6.3f} | {(rd + wr) / alg:5.3f} | {alg / dur / 1e6:7.2f} | {thr:5.1f} | {occ:5.1f} | {l2:5.1f}\n")
-        f.write("# stream_kernel<OP, BF16, VECB, UNROLL, BLOCK, LD, ST, PDL>: OP 0 add, 1 copy, 2 scale, 3 triad; fill_kernel<BF16, MODE>\n")
+        f.write("# stream_kernel<OP, BF16, VECB, UNROLL, BLOCK, LD, ST, PDL>: OP 0 add, 1 copy, 2 scale, 3 triad; fill_kernel<BF16, MODE, ALIGNED>\n")
         f.write("# (durations under ncu are single cold launches; the timed numbers are in the bench and sweep files)\n")
     print(open(dst).read())
 
