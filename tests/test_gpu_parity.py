@@ -404,3 +404,62 @@ def test_time_op_reports_device_times(L):
     assert 1000 < gbs < 12000, gbs           # an HBM3e part, and not a no-op
     for b in (dx, dy, dd):
         b.free()
+
+
+# ------------------------------------------------------------------------------------------------
+# Size-independent identities of the four operations, at BASELINE.json's full size (2^28 elements).  None of them
+# needs the oracle at that size: the two sides of each identity are computed by DIFFERENT kernels (or the generator's
+# own checksum, which the host loop supplies) and must agree bit for bit over the whole vector.
+
+@pytest.mark.parametrize("dtype", ["f32", "bf16"])
+def test_algebraic_identities_at_full_size(L, dtype):
+    n = 1 << 28
+    e = esz(dtype)
+    vp = C.c_void_p
+    start = (1 << 33) + 12                                      # global indices beyond 2^32
+    dx, dy, d1, d2 = (pkg.DeviceBuffer(n * e) for _ in range(4))
+    ws = pkg.DeviceBuffer(L.b200v_checksum_workspace_bytes())
+
+    def ck(buf):
+        return pkg.checksum(vp(buf.ptr), n * e, 0, ws)
+
+    def op(name, dst, x, y, s):
+        pkg.stream_op(name, dtype, vp(dst.ptr), vp(x.ptr), vp(y.ptr) if y is not None else None, s, n)
+
+    for mode in (O.GEN_BITS, O.GEN_UNIT):
+        pkg.check(L.b200v_fill(pkg.DTYPES[dtype], vp(dx.ptr), start, n, SEED, 0, mode, None))
+        pkg.check(L.b200v_fill(pkg.DTYPES[dtype], vp(dy.ptr), start, n, SEED, 1, mode, None))
+        cx, cy = ck(dx), ck(dy)
+        # the generator on the device == the generator on the host, over the whole vector
+        words = 4 // e
+        want = [0, 0]
+        for off in range(0, n, 1 << 24):
+            c = O.checksum(O.fill(dtype, start + off, 1 << 24, SEED, 0, mode), off // words, threads=0)
+            want = [(want[0] + c[0]) & M64, (want[1] + c[1]) & M64]
+        assert cx == tuple(want)
+        # copy is the identity, and idempotent
+        op("copy", d1, dx, None, 0.0)
+        assert ck(d1) == cx
+        op("copy", d2, d1, None, 0.0)
+        assert ck(d2) == cx
+        # scale by 1 is the identity (every finite value, denormals and signed zeros included)
+        op("scale", d1, dx, None, 1.0)
+        assert ck(d1) == cx
+        # addition commutes
+        op("add", d1, dx, dy, 0.0)
+        op("add", d2, dy, dx, 0.0)
+        c_add = ck(d1)
+        assert ck(d2) == c_add
+        # triad with s = 1 is the addition (one rounding either way)
+        op("triad", d2, dx, dy, 1.0)
+        assert ck(d2) == c_add
+        # doubling: 2 * x == x + x (exact, or the same overflow to infinity)
+        op("scale", d1, dx, None, 2.0)
+        op("add", d2, dx, dx, 0.0)
+        assert ck(d1) == ck(d2)
+        if mode == O.GEN_UNIT:
+            # triad with s = 0 returns the addend: fma(0, x, y) == y for x, y >= 0
+            op("triad", d1, dx, dy, 0.0)
+            assert ck(d1) == cy
+    for b in (dx, dy, d1, d2, ws):
+        b.free()
