@@ -18,13 +18,18 @@ def test_cited_profile_files_exist():
                 os.path.join("kubernetes-with-nvidia-gpu_b200", "csrc", "tuning.h"),
                 os.path.join("kubernetes-with-nvidia-gpu_b200", "csrc", "kernels.cu")):
         text = read(doc)
-        cited |= set(re.findall(r"(?:profiles/)?(r\d\d_[A-Za-z0-9_.{},*-]+|traffic\.json)", text))
+        cited |= set(re.findall(r"(?<![A-Za-z0-9_])(?:profiles/)?(r\d\d_[A-Za-z0-9_.{},*-]+|traffic\.json)", text))
     assert len(cited) > 15
     missing = []
     for c in sorted(cited):
         c = c.rstrip(".,")
-        m = re.search(r"\{([^}]*)\}", c)
-        names = [c[:m.start()] + alt + c[m.end():] for alt in m.group(1).split(",")] if m else [c]
+        names = [c]
+        while any("{" in n for n in names):          # expand every {a,b,c} group
+            out = []
+            for n in names:
+                m = re.search(r"\{([^{}]*)\}", n)
+                out += [n[:m.start()] + alt + n[m.end():] for alt in m.group(1).split(",")] if m else [n.replace("{", "")]
+            names = out
         for n in names:
             pattern = os.path.join(ROOT, "profiles", n if "." in os.path.basename(n) or "*" in n else n + "*")
             if not glob.glob(pattern):
