@@ -290,6 +290,34 @@ def test_vector_add_host_buffers(L, pinned):
     pkg.check(L.b200v_vector_add_host_release())
 
 
+def test_vector_add_host_with_registered_arrays_and_pipeline_shapes(L):
+    """Host arrays the caller already owns, pinned in place with b200v_host_register; and every chunking the pipeline
+    can be given (one chunk, a tail that is ramped down, chunk sizes that do not divide n) gives the same bits."""
+    n = (5 << 20) + 12345
+    a = O.fill("f32", 3, n, SEED, 0, O.GEN_BITS)
+    b = O.fill("f32", 3, n, SEED, 1, O.GEN_BITS)
+    c = np.zeros(n, dtype=np.uint32)
+    want = O.op("add", "f32", n, x=a, y=b)
+    vp = lambda arr: arr.ctypes.data_as(C.c_void_p)
+    for arr in (a, b, c):
+        pkg.check(L.b200v_host_register(vp(arr), arr.nbytes))
+    try:
+        for chunk_elems, slots in ((8 << 20, 3), (1 << 20, 2), (1 << 18, 4), ((1 << 20) + 24, 3), (1024, 8), (1 << 23, 1)):
+            pkg.check(L.b200v_vector_add_host_config(chunk_elems, slots))
+            c[:] = 0
+            pkg.check(L.b200v_vector_add_host(vp(a), vp(b), vp(c), n))
+            np.testing.assert_array_equal(c, want, err_msg=f"chunk {chunk_elems} slots {slots}")
+        # arguments are checked; the call is synchronous also when it fails
+        assert L.b200v_vector_add_host(None, vp(b), vp(c), n) == pkg.ERR_INVALID
+        assert L.b200v_vector_add_host_config(8, 3) == pkg.ERR_INVALID and L.b200v_vector_add_host_config(1 << 20, 0) == pkg.ERR_INVALID
+        assert L.b200v_host_register(None, 16) == pkg.ERR_INVALID
+    finally:
+        pkg.check(L.b200v_vector_add_host_config(8 << 20, 3))      # back to the defaults
+        pkg.check(L.b200v_vector_add_host_release())
+        for arr in (a, b, c):
+            pkg.check(L.b200v_host_unregister(vp(arr)))
+
+
 # ------------------------------------------------------------------------------------------------
 # BASELINE.json sizes: verified through the checksum property (shards of the host oracle's output
 # add up to the device's checksum) plus bit-exact windows brought back to the host.
