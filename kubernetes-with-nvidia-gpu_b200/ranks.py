@@ -30,8 +30,14 @@ class Ranks:
                 self.device = f"cuda:{self.local_rank}"
                 dist.init_process_group("nccl", device_id=torch.device(self.device))
                 # a second, CPU-only group for waits that must not put a kernel on the GPUs (an NCCL barrier
-                # parks a spinning kernel on every waiting rank's device)
-                self.host_group = dist.new_group(backend="gloo")
+                # parks a spinning kernel on every waiting rank's device).  One node only, so the loopback
+                # interface will do when the container's hostname does not resolve; if gloo cannot come up
+                # at all, host_barrier() falls back to the NCCL barrier.
+                os.environ.setdefault("GLOO_SOCKET_IFNAME", "lo")
+                try:
+                    self.host_group = dist.new_group(backend="gloo")
+                except Exception:
+                    self.host_group = None
             else:
                 dist.init_process_group(backend)
 
