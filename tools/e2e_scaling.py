@@ -14,8 +14,8 @@ ranks start each measurement together; the job's time is the max over ranks of t
            complex deliver with no kernel and no pipeline in the way;
   solo     each GPU alone, in turn (is every GPU's link the same?);
   pairs    GPU 0 together with each other GPU (which GPUs share an upstream path?);
-  host     what the host's DRAM gives the CPU: all W ranks copying 1 GiB at once with their share of the
-           host threads (the oracle's OpenMP copy / add loops, used here only as a bandwidth probe);
+  host     what the host's DRAM gives the CPU: all W ranks copying / adding 1 GiB arrays at once with their
+           share of the host threads (plain OpenMP loops, tools/hostbw.c);
   pipeline b200v_vector_add_host over chunk size x slots with N ranks at once: the e2e number itself,
            with cudaHostAlloc buffers and, once, with transparent-huge-page-backed registered buffers.
 
@@ -32,7 +32,6 @@ import time
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 world_env = int(os.environ.get("WORLD_SIZE", "1"))
 cores = len(os.sched_getaffinity(0))
@@ -202,18 +201,19 @@ if world > 1 and not quick:
         print("pairs", json.dumps(pairs), flush=True)
 
 # ---- host DRAM as the CPU sees it: all ranks copy / add 1 GiB arrays at once ----------------------------
-import oracle_lib as O  # noqa: E402  (memory-bandwidth probe only)
-OL = O.lib()
+HB = C.CDLL(os.path.join(ROOT, "tools", "libhostbw.so"))      # make -C tools
+HB.hostbw_copy.argtypes = [vp, vp, C.c_size_t, C.c_int]
+HB.hostbw_add.argtypes = [vp, vp, vp, C.c_size_t, C.c_int]
 src = np.full(N, 0x3F000000, dtype=np.uint32)
 dst = np.zeros(N, dtype=np.uint32)
 
 
 def host_copy():
-    OL.oracle_copy_f32(dst.ctypes.data_as(vp), src.ctypes.data_as(vp), N, threads)
+    HB.hostbw_copy(dst.ctypes.data_as(vp), src.ctypes.data_as(vp), N, threads)
 
 
 def host_add():
-    OL.oracle_add_f32(dst.ctypes.data_as(vp), src.ctypes.data_as(vp), hA.view(np.uint32).ctypes.data_as(vp), N, threads)
+    HB.hostbw_add(dst.ctypes.data_as(vp), src.ctypes.data_as(vp), hA.view(np.uint32).ctypes.data_as(vp), N, threads)
 
 
 t = job_seconds(host_copy)
