@@ -49,7 +49,12 @@ def test_no_oracle_in_product(L):
         for f in files:
             if f.endswith((".cu", ".cuh", ".cpp", ".h", ".py", "Makefile")):
                 src = open(os.path.join(dirpath, f)).read()
-                assert "liboracle" not in src and "oracle.h" not in src, f
+                assert "liboracle" not in src and "oracle.h" not in src and "oracle_lib" not in src, f
+    # the developer tools stay clear of it too: only tests/, __graft_entry__.smoke() and bench.py's CPU legs use the oracle
+    for f in os.listdir(os.path.join(ROOT, "tools")):
+        if f.endswith((".py", ".cu", ".c", ".sh", "Makefile")):
+            src = open(os.path.join(ROOT, "tools", f)).read()
+            assert "liboracle" not in src and "oracle.h" not in src and "oracle_lib" not in src, f
 
 
 def test_status_names_and_version(L):
