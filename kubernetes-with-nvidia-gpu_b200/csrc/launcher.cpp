@@ -5,14 +5,14 @@
 // `kubectl logs` (README:332-335), this binary lists the GPUs the container was granted
 // (README:315-317), runs a vectorAdd on the GPU, checks it bit for bit against a host loop, prints
 // `Test PASSED` or `Test FAILED` as the last verdict line and exits 0 / non-zero, which is what
-// `restartPolicy: OnFailure` (README:309) acts on.  With no arguments it does exactly that, on
-// device 0 only, well inside the 15 s the guide waits (README:326).
+// `restartPolicy: OnFailure` (README:309) acts on.  With no arguments it does exactly that, on every
+// GPU the pod was granted (one, under the reference's limit), well inside the 15 s the guide waits (README:326).
 //
 // All GPU work goes through the C ABI in include/b200v.h.  The host loops in hostcheck.cpp are the
 // verification half of the workload and the OpenMP baseline; there is no CPU fallback for the
 // GPU path: without a usable sm_100 device the verdict is FAILED.
 //
-//   gpu-validate                       vectorAdd N=50,000 on GPU 0          (BASELINE.json configs[0/1] contract)
+//   gpu-validate                       vectorAdd N=50,000 on every granted GPU (BASELINE.json configs[0/1] contract)
 //   gpu-validate --mode list           device discovery only (the nvidia-smi-style listing)
 //   gpu-validate --mode bench          STREAM copy/scale/add/triad sweep, fp32+bf16, + OpenMP baseline (configs[2])
 //   gpu-validate --mode node           one process per GPU, sharded triad, max over ranks       (configs[3])
@@ -149,22 +149,14 @@ int print_devices(int* count_out, bool all_details)
 // ----------------------------------------------------------------------------------------------
 // smoke: the cuda-samples vectorAdd flow — host arrays, H2D, kernel, D2H, host re-computation.
 
-int mode_smoke(const Args& a)
+// One GPU's share of the smoke test: H2D, kernel, D2H, bit-compare with the host loop's result.
+static int smoke_one_gpu(const Args& a, int device, const std::vector<float>& hA, const std::vector<float>& hB,
+                         const std::vector<float>& want, bool inject)
 {
-    printf("[gpu-validate] B200 validation workload (vectorAdd, fp32, %" PRIu64 " elements)\n", a.n);
-    int count = 0;
-    int st = print_devices(&count, false);
-    if (st != B200V_OK) return fail_status(st, "device discovery");
-    if (a.device >= count) return fail(EX_NO_DEVICE, "device %d requested, %d visible", a.device, count);
-    TRY(b200v_set_device(a.device));
-    TRY(b200v_require_sm100(a.device));
-
-    const size_t n = (size_t)a.n;
-    std::vector<float> hA(n), hB(n), hC(n), want(n);
-    hostcheck::fill(hostcheck::F32, hA.data(), 0, n, a.seed, 0, hostcheck::UNIT);
-    hostcheck::fill(hostcheck::F32, hB.data(), 0, n, a.seed, 1, hostcheck::UNIT);
-
-    printf("[vectorAdd] host -> device copy of A and B, kernel, device -> host copy of C (GPU %d)\n", a.device);
+    const size_t n = hA.size();
+    std::vector<float> hC(n);
+    TRY(b200v_set_device(device));
+    TRY(b200v_require_sm100(device));
     void *dA = nullptr, *dB = nullptr, *dC = nullptr;
     TRY(b200v_malloc(&dA, n * 4));
     TRY(b200v_malloc(&dB, n * 4));
@@ -178,22 +170,49 @@ int mode_smoke(const Args& a)
     TRY(b200v_free(dB));
     TRY(b200v_free(dC));
 
-    if (a.inject_fault && n) {
+    if (inject && n) {
         uint32_t u;
         memcpy(&u, &hC[n / 2], 4);
         u ^= 1u;   // one flipped bit in one element must turn the verdict
         memcpy(&hC[n / 2], &u, 4);
-        printf("[vectorAdd] --inject-fault: flipped the low bit of element %zu\n", n / 2);
+        printf("[vectorAdd] --inject-fault: flipped the low bit of element %zu (GPU %d)\n", n / 2, device);
     }
-    hostcheck::apply(hostcheck::ADD, hostcheck::F32, want.data(), hA.data(), hB.data(), 0.0f, n, false);
     const size_t bad = hostcheck::first_mismatch(hostcheck::F32, hC.data(), want.data(), n);
     if (bad != n) {
         uint32_t g, w;
         memcpy(&g, &hC[bad], 4);
         memcpy(&w, &want[bad], 4);
-        return fail(EX_MISMATCH, "result verification failed at element %zu: device 0x%08x, host loop 0x%08x", bad, g, w);
+        return fail(EX_MISMATCH, "result verification failed at element %zu on GPU %d: device 0x%08x, host loop 0x%08x", bad, device, g, w);
     }
-    printf("[vectorAdd] %zu of %zu elements bit-identical to the host loop\n", n, n);
+    printf("[vectorAdd] GPU %d: %zu of %zu elements bit-identical to the host loop\n", device, n, n);
+    (void)a;
+    return EX_PASS;
+}
+
+int mode_smoke(const Args& a)
+{
+    printf("[gpu-validate] B200 validation workload (vectorAdd, fp32, %" PRIu64 " elements)\n", a.n);
+    int count = 0;
+    int st = print_devices(&count, false);
+    if (st != B200V_OK) return fail_status(st, "device discovery");
+    if (a.device >= count) return fail(EX_NO_DEVICE, "device %d requested, %d visible", a.device, count);
+    // Every GPU the container was granted (resources.limits nvidia.com/gpu: N, README:315-317) is checked, one after
+    // the other; --device D restricts the run to one.  With the reference's limit of 1 that is GPU 0, as before.
+    const int first = a.device >= 0 ? a.device : 0;
+    const int last = a.device >= 0 ? a.device : count - 1;
+
+    const size_t n = (size_t)a.n;
+    std::vector<float> hA(n), hB(n), want(n);
+    hostcheck::fill(hostcheck::F32, hA.data(), 0, n, a.seed, 0, hostcheck::UNIT);
+    hostcheck::fill(hostcheck::F32, hB.data(), 0, n, a.seed, 1, hostcheck::UNIT);
+    hostcheck::apply(hostcheck::ADD, hostcheck::F32, want.data(), hA.data(), hB.data(), 0.0f, n, false);
+
+    printf("[vectorAdd] host -> device copy of A and B, kernel, device -> host copy of C, on %s\n",
+           first == last ? "one GPU" : "every visible GPU in turn");
+    for (int d = first; d <= last; ++d) {
+        const int rc = smoke_one_gpu(a, d, hA, hB, want, a.inject_fault && d == last);
+        if (rc != EX_PASS) return rc;
+    }
     return pass();
 }
 
@@ -289,7 +308,7 @@ void usage()
             "                    [--iters I] [--warmup W] [--seconds S] [--seed X] [--p2p-bytes B]\n"
             "                    [--min-log2-bytes a --max-log2-bytes b] [--measured-copy-gbs G] [--json FILE] [--inject-fault] [--fail-on-throttle]\n"
             "                    [--hbm-fraction F]   (burnin/full: arrays cover F of each GPU's free HBM instead of --log2n)\n"
-            "no arguments: vectorAdd N=50000 on GPU 0, prints Test PASSED / Test FAILED, exit code 0 / non-zero\n");
+            "no arguments: vectorAdd N=50000 on every visible GPU (--device D: one), prints Test PASSED / Test FAILED, exit code 0 / non-zero\n");
 }
 
 bool parse(int argc, char** argv, Args& a)

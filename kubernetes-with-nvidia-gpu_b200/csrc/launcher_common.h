@@ -35,7 +35,7 @@ constexpr double kNvlinkGBs = 900.0;     // per direction per GPU
 
 struct Args {
     std::string mode = "smoke";
-    int device = 0;
+    int device = -1;             // smoke: -1 = every visible GPU; shard children get their own
     uint64_t n = 50000;          // smoke: cuda-samples vectorAdd size
     bool n_set = false;
     int log2n = -1;

@@ -15,12 +15,13 @@ int mode_bench(const Args& a)
     int st = print_devices(&count, false);
     if (st != B200V_OK) return fail_status(st, "device discovery");
     if (a.device >= count) return fail(EX_NO_DEVICE, "device %d requested, %d visible", a.device, count);
-    TRY(b200v_set_device(a.device));
-    TRY(b200v_require_sm100(a.device));
-    b200v_device_info info;   // queried again now that a.device is current: free memory is filled in
+    const int device = a.device >= 0 ? a.device : 0;      // the sweep runs on one GPU: --device D, else GPU 0
+    TRY(b200v_set_device(device));
+    TRY(b200v_require_sm100(device));
+    b200v_device_info info;   // queried again now that the device is current: free memory is filled in
     memset(&info, 0, sizeof info);
     info.struct_size = sizeof info;
-    TRY(b200v_device_info_get(a.device, &info));
+    TRY(b200v_device_info_get(device, &info));
 
     int max_log2 = a.max_log2_bytes;
     while (max_log2 > a.min_log2_bytes && 3.2 * (double)(1ull << max_log2) > (double)info.hbm_free_bytes) --max_log2;

@@ -43,7 +43,12 @@ def test_default_pod_run(exe):
     assert last_line(r) == "Test PASSED"
     assert elapsed < 15.0, f"default run took {elapsed:.1f} s; the guide reads the log after `sleep 15` (reference README.md:326)"
     assert "NVIDIA B200" in r.stdout and "sm_100" in r.stdout
-    assert "50000 of 50000 elements bit-identical" in r.stdout
+    # every GPU the container was granted is checked (reference README.md:315-317: the limit decides what is visible)
+    assert r.stdout.count("50000 of 50000 elements bit-identical") == ngpus()
+    for d in range(ngpus()):
+        assert f"[vectorAdd] GPU {d}: 50000 of 50000" in r.stdout
+    one = run(exe, "--device", "0")
+    assert one.returncode == 0 and last_line(one) == "Test PASSED" and one.stdout.count("elements bit-identical") == 1
 
 
 def test_fault_injection_fails_the_pod(exe):
