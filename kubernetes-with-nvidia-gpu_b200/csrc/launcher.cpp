@@ -149,44 +149,65 @@ int print_devices(int* count_out, bool all_details)
 // ----------------------------------------------------------------------------------------------
 // smoke: the cuda-samples vectorAdd flow — host arrays, H2D, kernel, D2H, host re-computation.
 
-// One GPU's share of the smoke test: H2D, kernel, D2H, bit-compare with the host loop's result.
-static int smoke_one_gpu(const Args& a, int device, const std::vector<float>& hA, const std::vector<float>& hB,
-                         const std::vector<float>& want, bool inject)
+// One GPU's share of the smoke test: H2D, kernel, D2H, bit-compare with the host loop's result.  Runs on its own
+// host thread (one thread per device, as include/b200v.h asks), so it prints nothing: the outcome goes into `out`.
+struct SmokeOutcome {
+    int exit_code = EX_PASS;
+    std::string line;      // the per-GPU log line, or the failure reason
+};
+
+static void smoke_one_gpu(int device, const std::vector<float>& hA, const std::vector<float>& hB, const std::vector<float>& want,
+                          bool inject, SmokeOutcome& out)
 {
     const size_t n = hA.size();
     std::vector<float> hC(n);
-    TRY(b200v_set_device(device));
-    TRY(b200v_require_sm100(device));
     void *dA = nullptr, *dB = nullptr, *dC = nullptr;
-    TRY(b200v_malloc(&dA, n * 4));
-    TRY(b200v_malloc(&dB, n * 4));
-    TRY(b200v_malloc(&dC, n * 4));
-    TRY(b200v_memcpy_h2d(dA, hA.data(), n * 4, nullptr));
-    TRY(b200v_memcpy_h2d(dB, hB.data(), n * 4, nullptr));
-    TRY(b200v_add_f32((float*)dC, (const float*)dA, (const float*)dB, n, nullptr));
-    TRY(b200v_memcpy_d2h(hC.data(), dC, n * 4, nullptr));
-    TRY(b200v_device_sync());
-    TRY(b200v_free(dA));
-    TRY(b200v_free(dB));
-    TRY(b200v_free(dC));
+    char buf[512];
+    int st = B200V_OK;
+    const char* what = "";
+#define STEP(call)                         \
+    if (st == B200V_OK) {                  \
+        st = (call);                       \
+        if (st != B200V_OK) what = #call;  \
+    }
+    STEP(b200v_set_device(device));
+    STEP(b200v_require_sm100(device));
+    STEP(b200v_malloc(&dA, n * 4));
+    STEP(b200v_malloc(&dB, n * 4));
+    STEP(b200v_malloc(&dC, n * 4));
+    STEP(b200v_memcpy_h2d(dA, hA.data(), n * 4, nullptr));
+    STEP(b200v_memcpy_h2d(dB, hB.data(), n * 4, nullptr));
+    STEP(b200v_add_f32((float*)dC, (const float*)dA, (const float*)dB, n, nullptr));
+    STEP(b200v_memcpy_d2h(hC.data(), dC, n * 4, nullptr));
+    STEP(b200v_device_sync());
+#undef STEP
+    if (st != B200V_OK) {       // b200v_last_error() is per thread: read it here
+        snprintf(buf, sizeof buf, "GPU %d: %s: %s: %s", device, what, b200v_status_name(st), b200v_last_error());
+        out.exit_code = exit_code_for(st);
+        out.line = buf;
+    }
+    b200v_free(dA);
+    b200v_free(dB);
+    b200v_free(dC);
+    if (st != B200V_OK) return;
 
     if (inject && n) {
         uint32_t u;
         memcpy(&u, &hC[n / 2], 4);
         u ^= 1u;   // one flipped bit in one element must turn the verdict
         memcpy(&hC[n / 2], &u, 4);
-        printf("[vectorAdd] --inject-fault: flipped the low bit of element %zu (GPU %d)\n", n / 2, device);
     }
     const size_t bad = hostcheck::first_mismatch(hostcheck::F32, hC.data(), want.data(), n);
     if (bad != n) {
         uint32_t g, w;
         memcpy(&g, &hC[bad], 4);
         memcpy(&w, &want[bad], 4);
-        return fail(EX_MISMATCH, "result verification failed at element %zu on GPU %d: device 0x%08x, host loop 0x%08x", bad, device, g, w);
+        snprintf(buf, sizeof buf, "result verification failed at element %zu on GPU %d: device 0x%08x, host loop 0x%08x", bad, device, g, w);
+        out.exit_code = EX_MISMATCH;
+    } else {
+        snprintf(buf, sizeof buf, "[vectorAdd] GPU %d: %zu of %zu elements bit-identical to the host loop", device, n, n);
     }
-    printf("[vectorAdd] GPU %d: %zu of %zu elements bit-identical to the host loop\n", device, n, n);
-    (void)a;
-    return EX_PASS;
+    out.line = buf;
 }
 
 int mode_smoke(const Args& a)
@@ -196,8 +217,10 @@ int mode_smoke(const Args& a)
     int st = print_devices(&count, false);
     if (st != B200V_OK) return fail_status(st, "device discovery");
     if (a.device >= count) return fail(EX_NO_DEVICE, "device %d requested, %d visible", a.device, count);
-    // Every GPU the container was granted (resources.limits nvidia.com/gpu: N, README:315-317) is checked, one after
-    // the other; --device D restricts the run to one.  With the reference's limit of 1 that is GPU 0, as before.
+    // Every GPU the container was granted (resources.limits nvidia.com/gpu: N, README:315-317) is checked; --device D
+    // restricts the run to one.  With the reference's limit of 1 that is GPU 0, as before.  The GPUs are driven by one
+    // host thread each, at the same time: creating eight CUDA contexts one after the other would take most of the
+    // 15 s the guide waits before it reads the log (README:326).
     const int first = a.device >= 0 ? a.device : 0;
     const int last = a.device >= 0 ? a.device : count - 1;
 
@@ -208,11 +231,19 @@ int mode_smoke(const Args& a)
     hostcheck::apply(hostcheck::ADD, hostcheck::F32, want.data(), hA.data(), hB.data(), 0.0f, n, false);
 
     printf("[vectorAdd] host -> device copy of A and B, kernel, device -> host copy of C, on %s\n",
-           first == last ? "one GPU" : "every visible GPU in turn");
-    for (int d = first; d <= last; ++d) {
-        const int rc = smoke_one_gpu(a, d, hA, hB, want, a.inject_fault && d == last);
-        if (rc != EX_PASS) return rc;
-    }
+           first == last ? "one GPU" : "every visible GPU");
+    if (a.inject_fault && n) printf("[vectorAdd] --inject-fault: flipping the low bit of element %zu (GPU %d)\n", n / 2, last);
+    fflush(stdout);
+    std::vector<SmokeOutcome> outcome((size_t)(last - first + 1));
+    std::vector<std::thread> workers;
+    for (int d = first; d <= last; ++d)
+        workers.emplace_back(smoke_one_gpu, d, std::cref(hA), std::cref(hB), std::cref(want), a.inject_fault && d == last,
+                             std::ref(outcome[(size_t)(d - first)]));
+    for (auto& w : workers) w.join();
+    for (const auto& o : outcome)      // the log lists every GPU's result before the verdict
+        if (o.exit_code == EX_PASS) printf("%s\n", o.line.c_str());
+    for (const auto& o : outcome)
+        if (o.exit_code != EX_PASS) return fail(o.exit_code, "%s", o.line.c_str());
     return pass();
 }
 
