@@ -102,3 +102,45 @@ def test_our_arm_line():
     assert bi["elements_per_gpu"] > (1 << 32) and min(bi["passes_per_gpu"]) >= 2 and 3000 < bi["gbs_per_gpu"] < 12000
     assert bi["under_load"][0]["power_max_w"] > 200
     assert d["p2p"] is None          # one GPU: no pair to check
+
+
+def _bench_module():
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("bench_mod", os.path.join(ROOT, "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    return bench
+
+
+def test_clock_sampler_windows():
+    """The NVML window logic with synthetic samples: a leg's summary covers exactly the samples between its marks;
+    the headline window widens to the loaded stretch when the timed region is shorter than three samples."""
+    bench = _bench_module()
+    s = bench.ClockSampler.__new__(bench.ClockSampler)       # no NVML in this tier: fill the fields by hand
+    s.ok, s.sm_max, s.marks = True, 1965, {}
+    s.samples = [(t * 0.01, 1965 if t < 50 else 1700, 0 if t < 50 else 0x4, 200.0 if t < 50 else 990.0) for t in range(100)]
+    s.marks.update(load_start=0.10, timed_start=0.20, timed_end=0.215, load_end=0.40, sustained_add_start=0.60, sustained_add_end=0.90)
+    head = s.summary()
+    assert head["samples"] == 31 and "shorter than 3 samples" in head["window"] and head["sm_mhz"] == 1965 and head["reasons"] == []
+    leg = s.summary("sustained_add_start", "sustained_add_end", widen=None)
+    assert leg["samples"] == 31 and leg["sm_mhz"] == 1700 and leg["sm_mhz_min"] == 1700 and leg["reasons"] == ["sw_power_cap"]
+    assert leg["power_w_max"] == 990.0 and leg["window"] == "sustained_add_start .. sustained_add_end"
+    s.marks.update(timed_end=0.30)
+    assert s.summary()["samples"] == 11 and s.summary()["window"] == "timed_start .. timed_end"
+    s.ok = False
+    s.err = "no NVML"
+    assert s.summary()["sm_mhz"] is None and "NVML unavailable" in s.summary()["note"]
+
+
+def test_committed_launch_summary_matches_its_raw_list(tmp_path):
+    """profiles/r02_ncu_launches_summary.txt is what tools/ncu_summarise.py makes of the committed raw ncu launch list."""
+    raw = os.path.join(ROOT, "profiles", "r02_ncu_launches_raw.csv")
+    out = tmp_path / "summary.txt"
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "ncu_summarise.py"), "launches", raw, str(out)],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    fresh = [ln for ln in out.read_text().splitlines() if not ln.startswith("#")]
+    kept = [ln for ln in open(os.path.join(ROOT, "profiles", "r02_ncu_launches_summary.txt")).read().splitlines() if not ln.startswith("#")]
+    assert fresh == kept and len(fresh) >= 5
+    big_add = next(ln for ln in fresh if "stream_kernel<0, 0, 32, 4, 512, 0, 0, 1>" in ln)
+    assert 440 < float(big_add.split("x")[1].split("us")[0]) < 460           # the headline kernel: ~0.45 ms per launch under ncu too
