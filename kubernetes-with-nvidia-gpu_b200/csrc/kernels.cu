@@ -154,8 +154,9 @@ __device__ __forceinline__ uint32_t gen_bf16_bits(uint32_t key, uint64_t index, 
     return b;
 }
 
-// The fill is integer-ALU bound (ncu: ALU pipe 94 %, DRAM 70 % for fp32 — profiles/r02_ncu_all_kernels.txt), so the
-// vector body spends as few ALU-pipe instructions per element as the integer spec allows:
+// The fill was integer-ALU bound (ncu on the round-1 shape: ALU pipe 94 % busy, DRAM 70 % for fp32), so the vector body
+// spends as few ALU-pipe instructions per element as the integer spec allows (now DRAM 83 % for fp32, 68 % for bf16:
+// profiles/r02_ncu_all_kernels.txt):
 //  * the generator mode is a template parameter;
 //  * the hash's high-half term is hoisted out of the per-element work (32-bit index arithmetic; a vector that
 //    straddles a 2^32 index boundary takes the plain path);
