@@ -288,33 +288,33 @@ def run_reference(args, rank):
 # ------------------------------------------------------------------------------------------------
 # rank 0: the product's own binaries as subprocesses (native shard launcher, NVLink check)
 
-def run_native(pkg, mode_args, json_name, timeout, json_path=None):
-    """Runs gpu-validate with --json; returns a dict: rc, verdict line, parsed json (or None), summary lines."""
-    with tempfile.TemporaryDirectory() as td:
-        js = json_path or os.path.join(td, json_name)
-        cmd = [pkg.LAUNCHER_PATH, *mode_args, "--json", js]
-        env = dict(os.environ, OMP_NUM_THREADS=str(host_cores()))     # torchrun exports OMP_NUM_THREADS=1
-        t0 = time.perf_counter()
-        try:
-            r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, env=env)
-            rc, out = r.returncode, r.stdout
-        except subprocess.TimeoutExpired:
-            rc, out = -1, f"timed out after {timeout} s"
-        wall = time.perf_counter() - t0
-        lines = out.strip().splitlines()
-        data = None
-        try:
-            with open(js) as f:
-                data = json.load(f)
-        except Exception:
-            pass
-        return {"rc": rc, "verdict": lines[-1] if lines else "", "json": data, "wall_s": round(wall, 1),
-                "summary_lines": [ln for ln in lines if ln.startswith(("[node]", "[p2p]", "reason:"))],
-                "cmd": "gpu-validate " + " ".join(mode_args)}
+def run_native(pkg, mode_args, js, timeout):
+    """Runs gpu-validate with --json js; returns a dict: rc, verdict line, parsed json (or None), summary lines."""
+    cmd = [pkg.LAUNCHER_PATH, *mode_args, "--json", js]
+    env = dict(os.environ, OMP_NUM_THREADS=str(host_cores()))     # torchrun exports OMP_NUM_THREADS=1
+    t0 = time.perf_counter()
+    try:
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, env=env)
+        rc, out = r.returncode, r.stdout
+    except subprocess.TimeoutExpired:
+        rc, out = -1, f"timed out after {timeout} s"
+    wall = time.perf_counter() - t0
+    lines = out.strip().splitlines()
+    data = None
+    try:
+        with open(js) as f:
+            data = json.load(f)
+    except Exception:
+        pass
+    return {"rc": rc, "verdict": lines[-1] if lines else "", "json": data, "wall_s": round(wall, 1),
+            "summary_lines": [ln for ln in lines if ln.startswith(("[node]", "[p2p]", "reason:"))],
+            "cmd": "gpu-validate " + " ".join(mode_args)}
 
 
 def native_node_leg(pkg, world, iters):
-    r = run_native(pkg, ["--mode", "node", "--gpus", str(world), "--log2n", str(SHARDED_LOG2), "--iters", str(iters)], "node.json", 600)
+    with tempfile.TemporaryDirectory() as td:
+        r = run_native(pkg, ["--mode", "node", "--gpus", str(world), "--log2n", str(SHARDED_LOG2), "--iters", str(iters)],
+                       os.path.join(td, "node.json"), 600)
     d = r.pop("json")
     out = dict(r, what="the pod entrypoint's per-GPU shard launcher (fork/exec one child per GPU, pipe start barrier, max over ranks), "
                        f"triad over 2^{SHARDED_LOG2} fp32 elements in total (BASELINE.json configs[3]); every shard verified against the host loop's checksum")
@@ -338,7 +338,7 @@ def native_full_leg(pkg, world, p2p_bytes, seconds, hbm_fraction):
             "--fail-on-throttle", "--p2p-bytes", str(p2p_bytes), "--iters", "12"]
     with tempfile.TemporaryDirectory() as td:
         js = os.path.join(td, "full.json")
-        r = run_native(pkg, args, "full.json", 800, json_path=js)
+        r = run_native(pkg, args, js, 800)
         try:
             with open(js + ".p2p") as f:
                 pj = json.load(f)
